@@ -1,0 +1,68 @@
+"""ctypes binding of libkvedge_b200.so (the C ABI in include/kvedge_b200.h).
+
+Loading never falls back to anything: a missing library raises, and every compute entry
+returns KV_ENODEVICE on a machine without a CUDA device.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libkvedge_b200.so")
+
+KV_OK, KV_EINVAL, KV_ENODEVICE, KV_ECUDA, KV_ENOMEM, KV_ECORRUPT, KV_ETEMPLATE = 0, -1, -2, -3, -4, -5, -6
+
+# name -> (restype, argtypes); every symbol declared in include/kvedge_b200.h
+SIGNATURES = {
+    "kv_version": (C.c_int, []),
+    "kv_last_error": (C.c_char_p, []),
+    "kv_device_count": (C.c_int, []),
+    "kv_b64enc_len": (C.c_size_t, [C.c_size_t]),
+    "kv_b64dec_maxlen": (C.c_size_t, [C.c_size_t]),
+    "kv_b64_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
+    "kv_b64enc_batch_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "kv_b64dec_batch_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                                      C.c_void_p]),
+    "kv_b64enc": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p]),
+    "kv_b64enc_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "kv_b64dec": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.POINTER(C.c_size_t),
+                            C.POINTER(C.c_size_t)]),
+    "kv_b64dec_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
+                                  C.c_void_p, C.c_void_p]),
+    "kv_set_device": (C.c_int, [C.c_int]),
+    "kv_shutdown": (None, []),
+}
+
+
+class KvError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"kvedge_b200 error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """The loaded library; raises if it has not been built (no silent fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: run `python -m kvedge_b200.build` "
+                "(or __graft_entry__.build()); there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != KV_OK:
+        raise KvError(rc, lib().kv_last_error().decode("utf-8", "replace"))

@@ -1,0 +1,511 @@
+// Batched standard-base64 encode / decode for sm_100a (B200).
+//
+// The hot path of levi106/kvedge's only byte transform: Sprig `b64enc` at
+//   deployment/helm/templates/aziot-edge-runtime-config-secret.yaml:6
+//   deployment/helm/templates/aziot-edge-vm-cloud-init-secret.yaml:6
+// and its inverse (Kubernetes decoding Secret.data.userdata for the disk read at
+// deployment/helm/templates/_helper.tpl:64,73).  Semantics are Go's
+// encoding/base64.StdEncoding (RFC 4648 section 4 alphabet, '=' padding, no wrapping).
+//
+// Shape of the work: many independent units (one Secret payload each) of ragged
+// length in one packed blob.  It is HBM-bound byte work -- 1 byte read and 4/3 bytes
+// written per input byte -- so the design goals are coalesced 16-byte stores, enough
+// bytes in flight per SM, and an ALU/FMA-pipe balanced sextet->ASCII mapping with no
+// table lookups.  No tensor cores: nothing here is a GEMM.
+//
+//   plan_count / plan_emit   ragged units -> fixed-size tiles (TileDesc table in scratch)
+//   b64enc_tiles             persistent grid, one tile per block iteration
+//   b64dec_tiles             canonical input fast path; anything else is flagged ...
+//   b64dec_slow              ... and re-decoded sequentially with Go's exact semantics
+#include "b64_kernels.cuh"
+
+namespace kvedge {
+
+// ----------------------------------------------------------------------------- layout
+ScratchLayout scratch_layout(int64_t n_units, int64_t total_in_bytes, int tile_in) {
+    ScratchLayout L;
+    if (n_units < 0) n_units = 0;
+    if (total_in_bytes < 0) total_in_bytes = 0;
+    L.n_plan_blocks = (n_units + kPlanBlock - 1) / kPlanBlock;
+    L.max_tiles = total_in_bytes / tile_in + n_units;
+    L.block_sums_off = 256;
+    size_t bs = (size_t)L.n_plan_blocks * sizeof(int32_t);
+    L.desc_off = (L.block_sums_off + bs + 255) / 256 * 256;
+    L.total = L.desc_off + (size_t)L.max_tiles * sizeof(TileDesc) + 256;
+    return L;
+}
+
+// ----------------------------------------------------------------------------- plan
+__device__ __forceinline__ int warp_incl_scan(int v) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, v, d);
+        if ((threadIdx.x & 31) >= d) v += t;
+    }
+    return v;
+}
+
+// Exclusive scan of one int per thread across a 1024-thread block; returns the
+// exclusive prefix and stores the block total in *total.
+__device__ __forceinline__ int block_excl_scan(int v, int *total) {
+    __shared__ int warp_sums[32];
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int incl = warp_incl_scan(v);
+    if (lane == 31) warp_sums[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int s = warp_sums[lane];
+        int si = warp_incl_scan(s);
+        warp_sums[lane] = si - s;  // exclusive prefix of each warp
+        if (lane == 31) *total = si;
+    }
+    __syncthreads();
+    return incl - v + warp_sums[wid];
+}
+
+__global__ void __launch_bounds__(kPlanBlock)
+plan_count(const int64_t *__restrict__ in_off, int64_t n_units, int tile_in,
+           int *__restrict__ block_sums) {
+    __shared__ int total;
+    int64_t u = (int64_t)blockIdx.x * kPlanBlock + threadIdx.x;
+    int cnt = 0;
+    if (u < n_units) {
+        int64_t len = in_off[u + 1] - in_off[u];
+        cnt = len > 0 ? (int)((len + tile_in - 1) / tile_in) : 0;
+    }
+    (void)block_excl_scan(cnt, &total);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+// MODE 0: encode (out step 4 bytes per 3 in). MODE 1: decode (3 per 4) + status init.
+template <int MODE>
+__global__ void __launch_bounds__(kPlanBlock)
+plan_emit(const int64_t *__restrict__ in_off, const int64_t *__restrict__ out_off,
+          int64_t n_units, int tile_in, const int *__restrict__ block_sums,
+          int *__restrict__ header, TileDesc *__restrict__ desc,
+          int64_t *__restrict__ out_len, int64_t *__restrict__ status) {
+    __shared__ int total;
+    __shared__ int base_sh;
+    __shared__ int red[32];
+    // tiles emitted by all earlier plan blocks
+    int part = 0;
+    for (int b = threadIdx.x; b < (int)blockIdx.x; b += kPlanBlock) part += block_sums[b];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = part;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        int s = red[threadIdx.x];
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+        if (threadIdx.x == 0) base_sh = s;
+    }
+    __syncthreads();
+
+    int64_t u = (int64_t)blockIdx.x * kPlanBlock + threadIdx.x;
+    int cnt = 0;
+    int64_t ibeg = 0, len = 0, obeg = 0;
+    if (u < n_units) {
+        ibeg = in_off[u];
+        len = in_off[u + 1] - ibeg;
+        if (len < 0) len = 0;
+        obeg = out_off[u];
+        cnt = len > 0 ? (int)((len + tile_in - 1) / tile_in) : 0;
+        if (MODE == 1) {
+            out_len[u] = len / 4 * 3;
+            status[u] = (len & 3) ? -2 : -1;  // -2: not canonical -> b64dec_slow decides
+        }
+    }
+    int first = base_sh + block_excl_scan(cnt, &total);
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) header[0] = base_sh + total;
+    for (int k = 0; k < cnt; ++k) {
+        int64_t s = (int64_t)k * tile_in;
+        TileDesc d;
+        d.in_pos = ibeg + s;
+        d.out_pos = obeg + (MODE == 0 ? s / 3 * 4 : s / 4 * 3);
+        int64_t rem = len - s;
+        d.len = (int32_t)(rem < tile_in ? rem : tile_in);
+        d.unit = (int32_t)u;
+        d.flags = (k == cnt - 1) ? 1 : 0;
+        d.pad = 0;
+        desc[first + k] = d;
+    }
+}
+
+// ----------------------------------------------------------------------------- encode
+// np = b0<<24 | b1<<16 | b2<<8 | (don't care).  Returns the four 6-bit values of the
+// 24-bit group, one per byte lane, first character in the lowest lane.
+__device__ __forceinline__ uint32_t sextets(uint32_t np) {
+    uint32_t x = np >> 26;
+    x |= (np >> 12) & 0x00003F00u;
+    x |= (np << 2) & 0x003F0000u;
+    x |= (np << 16) & 0x3F000000u;
+    return x;
+}
+
+// Four 6-bit values (one per byte lane) -> four RFC 4648 alphabet characters, branch
+// and table free.  Per lane:  c = v - 25 + 6[v>25] + 75[v<=51] + 15[v<=61] + 3[v>62].
+// The comparisons are carries into bit 7 of each lane (no lane ever overflows), and
+// the weighted flags are folded in with multiply-high, which runs on the FMA pipe and
+// leaves the ALU pipe for the adds and masks.  The lane sums end in [43, 122], so the
+// 32-bit arithmetic never lets one lane disturb the next.
+__device__ __forceinline__ uint32_t sextets_to_ascii(uint32_t x) {
+    uint32_t p1 = (x + 0x66666666u) & 0x80808080u;  // v > 25
+    uint32_t p2 = (0xB3B3B3B3u - x) & 0x80808080u;  // v <= 51
+    uint32_t p3 = (0xBDBDBDBDu - x) & 0x80808080u;  // v <= 61
+    uint32_t p4 = (x + 0x41414141u) & 0x80808080u;  // v > 62
+    uint32_t r = x - 0x19191919u;
+    r += __umulhi(p1, 6u << 25);
+    r += __umulhi(p2, 75u << 25);
+    r += __umulhi(p3, 15u << 25);
+    r += __umulhi(p4, 3u << 25);
+    return r;
+}
+
+// 12 input bytes in three little-endian words -> 16 output characters.
+__device__ __forceinline__ uint4 encode12(uint32_t a0, uint32_t a1, uint32_t a2) {
+    uint4 r;
+    r.x = sextets_to_ascii(sextets(__byte_perm(a0, 0u, 0x0124)));
+    r.y = sextets_to_ascii(sextets(__byte_perm(a0, a1, 0x3455)));
+    r.z = sextets_to_ascii(sextets(__byte_perm(a1, a2, 0x2344)));
+    r.w = sextets_to_ascii(sextets(__byte_perm(a2, 0u, 0x1233)));
+    return r;
+}
+
+__device__ __forceinline__ void store_chars(char *dst, uint4 v, int nchars) {
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+            if (g * 4 + b < nchars) dst[g * 4 + b] = (char)((w[g] >> (8 * b)) & 0xFF);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+b64enc_tiles(const uint8_t *__restrict__ in, char *__restrict__ out,
+             const TileDesc *__restrict__ desc, const int *__restrict__ header,
+             const int64_t *__restrict__ in_off, int64_t n_units) {
+    const int n_tiles = header[0];
+    const int64_t in_end = in_off[n_units];
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int4 *dp = reinterpret_cast<const int4 *>(desc + tile);
+        const int4 d0 = __ldg(dp), d1 = __ldg(dp + 1);
+        const int64_t in_pos = ((int64_t)(uint32_t)d0.y << 32) | (uint32_t)d0.x;
+        const int64_t out_pos = ((int64_t)(uint32_t)d0.w << 32) | (uint32_t)d0.z;
+        const int len = d1.x;
+        const uint8_t *src = in + in_pos;
+        char *dst = out + out_pos;
+        const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 3u);
+        const uint32_t dalign = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
+#pragma unroll
+        for (int row = 0; row < kEncTileIn / (kThreads * 12); ++row) {
+            const int off = row * (kThreads * 12) + (int)threadIdx.x * 12;
+            if (off >= len) break;
+            const uint8_t *p = src + off;
+            char *q = dst + (row * (kThreads * 16) + (int)threadIdx.x * 16);
+            // Word loads may touch up to 3 bytes before and 4 after this thread's 12;
+            // keep them inside the blob.
+            const bool interior = (off + 12 <= len) && (in_pos + off + 16 <= in_end) &&
+                                  (in_pos + off >= 3);
+            if (interior) {
+                const uint32_t *wp = reinterpret_cast<const uint32_t *>(p - sh);
+                uint32_t a0 = __ldg(wp), a1 = __ldg(wp + 1), a2 = __ldg(wp + 2);
+                if (sh) {
+                    uint32_t a3 = __ldg(wp + 3);
+                    const uint32_t s8 = sh * 8;
+                    a0 = __funnelshift_r(a0, a1, s8);
+                    a1 = __funnelshift_r(a1, a2, s8);
+                    a2 = __funnelshift_r(a2, a3, s8);
+                }
+                const uint4 v = encode12(a0, a1, a2);
+                if (dalign == 0) {
+                    *reinterpret_cast<uint4 *>(q) = v;
+                } else if ((dalign & 3u) == 0) {
+                    uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
+                    q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
+                } else {
+                    store_chars(q, v, 16);
+                }
+            } else {
+                // Edge thread: the unit's tail (fewer than 12 bytes, '=' padding) or a
+                // thread whose word loads would leave the blob. Byte loads.
+                const int nvalid = (len - off) < 12 ? (len - off) : 12;
+                uint32_t a[3] = {0u, 0u, 0u};
+#pragma unroll
+                for (int i = 0; i < 12; ++i)
+                    if (i < nvalid) a[i >> 2] |= (uint32_t)p[i] << (8 * (i & 3));
+                uint4 v = encode12(a[0], a[1], a[2]);
+                const int rem = nvalid % 3, gi = nvalid / 3;
+                if (rem) {
+                    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int g = 0; g < 4; ++g)
+                        if (g == gi)
+                            w[g] = (rem == 1) ? ((w[g] & 0x0000FFFFu) | 0x3D3D0000u)
+                                              : ((w[g] & 0x00FFFFFFu) | 0x3D000000u);
+                    v = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+                store_chars(q, v, (nvalid + 2) / 3 * 4);
+            }
+        }
+    }
+}
+
+// ----------------------------------------------------------------------------- decode
+// One alphabet character -> its 6-bit value, or a value >= 64 if it is not in the
+// alphabet.
+__device__ __forceinline__ uint32_t dec6(uint32_t c) {
+    uint32_t v = 0x80u;
+    if (c - 65u < 26u) v = c - 65u;
+    if (c - 97u < 26u) v = c - 71u;
+    if (c - 48u < 10u) v = c + 4u;
+    if (c == 43u) v = 62u;
+    if (c == 47u) v = 63u;
+    return v;
+}
+
+// Four characters (little-endian word) -> 24-bit group as bytes b0 | b1<<8 | b2<<16;
+// bit 31 of the result is set if any character was outside the alphabet.
+__device__ __forceinline__ uint32_t decode4(uint32_t w) {
+    uint32_t v0 = dec6(w & 0xFFu), v1 = dec6((w >> 8) & 0xFFu);
+    uint32_t v2 = dec6((w >> 16) & 0xFFu), v3 = dec6(w >> 24);
+    uint32_t bad = (v0 | v1 | v2 | v3) & 0x80u;
+    uint32_t n = (v0 << 18) | (v1 << 12) | (v2 << 6) | v3;  // 24-bit big-endian value
+    uint32_t r = __byte_perm(n, 0u, 0x4012);                 // -> b0 | b1<<8 | b2<<16
+    return r | (bad << 24);
+}
+
+__global__ void __launch_bounds__(kThreads)
+b64dec_tiles(const char *__restrict__ in, uint8_t *__restrict__ out,
+             const TileDesc *__restrict__ desc, const int *__restrict__ header,
+             const int64_t *__restrict__ in_off, int64_t n_units,
+             int64_t *__restrict__ out_len, int64_t *__restrict__ status) {
+    const int n_tiles = header[0];
+    const int64_t in_end = in_off[n_units];
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int4 *dp = reinterpret_cast<const int4 *>(desc + tile);
+        const int4 d0 = __ldg(dp), d1 = __ldg(dp + 1);
+        const int64_t in_pos = ((int64_t)(uint32_t)d0.y << 32) | (uint32_t)d0.x;
+        const int64_t out_pos = ((int64_t)(uint32_t)d0.w << 32) | (uint32_t)d0.z;
+        const int len = d1.x;
+        const int unit = d1.y;
+        const bool last_tile = (d1.z & 1) != 0;
+        const uint8_t *src = reinterpret_cast<const uint8_t *>(in) + in_pos;
+        uint8_t *dst = out + out_pos;
+        const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 3u);
+        const bool dst4 = (reinterpret_cast<uintptr_t>(dst) & 3u) == 0;
+        if (len & 3) continue;  // unit length not a multiple of 4: plan flagged it (-2)
+#pragma unroll
+        for (int row = 0; row < kDecTileIn / (kThreads * 16); ++row) {
+            const int off = row * (kThreads * 16) + (int)threadIdx.x * 16;
+            if (off >= len) break;
+            const uint8_t *p = src + off;
+            uint8_t *q = dst + (row * (kThreads * 12) + (int)threadIdx.x * 12);
+            const int nvalid = (len - off) < 16 ? (len - off) : 16;  // multiple of 4
+            uint32_t w[4] = {0x41414141u, 0x41414141u, 0x41414141u, 0x41414141u};
+            const bool interior = (nvalid == 16) && (in_pos + off + 20 <= in_end) &&
+                                  (in_pos + off >= 3);
+            if (interior) {
+                const uint32_t *wp = reinterpret_cast<const uint32_t *>(p - sh);
+                w[0] = __ldg(wp); w[1] = __ldg(wp + 1); w[2] = __ldg(wp + 2); w[3] = __ldg(wp + 3);
+                if (sh) {
+                    uint32_t w4 = __ldg(wp + 4);
+                    const uint32_t s8 = sh * 8;
+                    w[0] = __funnelshift_r(w[0], w[1], s8);
+                    w[1] = __funnelshift_r(w[1], w[2], s8);
+                    w[2] = __funnelshift_r(w[2], w[3], s8);
+                    w[3] = __funnelshift_r(w[3], w4, s8);
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    if (i < nvalid) {
+                        uint32_t m = 0xFFu << (8 * (i & 3));
+                        w[i >> 2] = (w[i >> 2] & ~m) | ((uint32_t)p[i] << (8 * (i & 3)));
+                    }
+            }
+            // '=' padding is legal only in the last quantum of the unit.
+            int npad = 0;
+            const int nq = nvalid >> 2;
+            if (last_tile && off + nvalid == len) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g)
+                    if (g == nq - 1) {
+                        if ((w[g] >> 24) == 0x3Du) {
+                            npad = 1;
+                            w[g] = (w[g] & 0x00FFFFFFu) | 0x41000000u;
+                            if (((w[g] >> 16) & 0xFFu) == 0x3Du) {
+                                npad = 2;
+                                w[g] = (w[g] & 0xFF00FFFFu) | 0x00410000u;
+                            }
+                        }
+                    }
+                out_len[unit] = (int64_t)(in_pos - in_off[unit] + off + nvalid) / 4 * 3 - npad;
+            }
+            uint32_t g0 = decode4(w[0]), g1 = decode4(w[1]), g2 = decode4(w[2]), g3 = decode4(w[3]);
+            if ((g0 | g1 | g2 | g3) & 0x80000000u) {
+                status[unit] = -2;  // benign race: every writer stores the same value
+                continue;
+            }
+            g0 &= 0xFFFFFFu; g1 &= 0xFFFFFFu; g2 &= 0xFFFFFFu; g3 &= 0xFFFFFFu;
+            const uint32_t o0 = g0 | (g1 << 24);
+            const uint32_t o1 = (g1 >> 8) | (g2 << 16);
+            const uint32_t o2 = (g2 >> 16) | (g3 << 8);
+            const int nbytes = nq * 3 - npad;
+            if (dst4 && nbytes == 12) {
+                uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
+                q4[0] = o0; q4[1] = o1; q4[2] = o2;
+            } else {
+                const uint32_t o[3] = {o0, o1, o2};
+#pragma unroll
+                for (int i = 0; i < 12; ++i)
+                    if (i < nbytes) q[i] = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
+            }
+        }
+    }
+}
+
+// Sequential decode of the units the fast path flagged (status == -2): '\r'/'\n'
+// inside the text, padding in odd places, characters outside the alphabet, lengths
+// that are not a multiple of four.  Follows Go's encoding/base64 decodeQuantum
+// (padded, non-strict) step by step so that both the bytes and the reported
+// CorruptInputError offset are Go's.  One thread per flagged unit: this is the
+// cold path (Kubernetes Secrets are canonical).
+__device__ __forceinline__ bool is_nl(uint8_t c) { return c == '\n' || c == '\r'; }
+
+__global__ void b64dec_slow(const char *__restrict__ in, const int64_t *__restrict__ in_off,
+                            int64_t n_units, uint8_t *__restrict__ out,
+                            const int64_t *__restrict__ out_off, int64_t *__restrict__ out_len,
+                            int64_t *__restrict__ status) {
+    for (int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; u < n_units;
+         u += (int64_t)gridDim.x * blockDim.x) {
+        if (status[u] != -2) continue;
+        const uint8_t *src = reinterpret_cast<const uint8_t *>(in) + in_off[u];
+        const int64_t len = in_off[u + 1] - in_off[u];
+        uint8_t *dst = out + out_off[u];
+        int64_t si = 0, n = 0, err = -1;
+        bool done = false;
+        while (!done) {
+            uint32_t dbuf[4] = {0, 0, 0, 0};
+            int dlen = 4;
+            bool end = false;
+            for (int j = 0; j < 4; ++j) {
+                if (si == len) {
+                    if (j != 0) err = si - j;
+                    dlen = 0;
+                    done = true;
+                    break;
+                }
+                uint8_t c = src[si++];
+                uint32_t v = dec6(c);
+                if (v < 64u) { dbuf[j] = v; continue; }
+                if (is_nl(c)) { --j; continue; }
+                if (c != '=') { err = si - 1; dlen = 0; done = true; break; }
+                if (j < 2) { err = si - 1; dlen = 0; done = true; break; }
+                if (j == 2) {
+                    while (si < len && is_nl(src[si])) ++si;
+                    if (si == len) { err = len; dlen = 0; done = true; break; }
+                    if (src[si] != '=') { err = si - 1; dlen = 0; done = true; break; }
+                    ++si;
+                }
+                while (si < len && is_nl(src[si])) ++si;
+                if (si < len) err = si;  // trailing garbage (bytes of this quantum are kept)
+                dlen = j;
+                end = true;
+                break;
+            }
+            if (dlen >= 2) {
+                uint32_t val = (dbuf[0] << 18) | (dbuf[1] << 12) | (dbuf[2] << 6) | dbuf[3];
+                dst[n] = (uint8_t)(val >> 16);
+                if (dlen >= 3) dst[n + 1] = (uint8_t)(val >> 8);
+                if (dlen >= 4) dst[n + 2] = (uint8_t)val;
+                n += dlen - 1;
+            }
+            if (end) done = true;
+        }
+        out_len[u] = n;
+        status[u] = err;  // -1 when the unit decoded cleanly
+    }
+}
+
+// ----------------------------------------------------------------------------- launchers
+static int g_occ_enc = 0, g_occ_dec = 0;
+
+static cudaError_t plan(const int64_t *d_in_off, const int64_t *d_out_off, int64_t n_units,
+                        int tile_in, int mode, const ScratchLayout &L, void *d_scratch,
+                        int64_t *d_out_len, int64_t *d_status, cudaStream_t stream) {
+    char *base = static_cast<char *>(d_scratch);
+    int *header = reinterpret_cast<int *>(base);
+    int *block_sums = reinterpret_cast<int *>(base + L.block_sums_off);
+    TileDesc *desc = reinterpret_cast<TileDesc *>(base + L.desc_off);
+    unsigned nb = (unsigned)L.n_plan_blocks;
+    plan_count<<<nb, kPlanBlock, 0, stream>>>(d_in_off, n_units, tile_in, block_sums);
+    if (mode == 0)
+        plan_emit<0><<<nb, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in,
+                                                    block_sums, header, desc, nullptr, nullptr);
+    else
+        plan_emit<1><<<nb, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in,
+                                                    block_sums, header, desc, d_out_len, d_status);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_b64enc(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
+                          int64_t total_in_bytes, char *d_out, const int64_t *d_out_off,
+                          void *d_scratch, size_t scratch_bytes, cudaStream_t stream,
+                          int sm_count) {
+    if (n_units <= 0) return cudaSuccess;
+    ScratchLayout L = scratch_layout(n_units, total_in_bytes, kEncTileIn);
+    if (scratch_bytes < L.total) return cudaErrorInvalidValue;
+    cudaError_t e = plan(d_in_off, d_out_off, n_units, kEncTileIn, 0, L, d_scratch, nullptr,
+                         nullptr, stream);
+    if (e != cudaSuccess) return e;
+    if (g_occ_enc == 0) {
+        int occ = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, b64enc_tiles, kThreads, 0);
+        if (e != cudaSuccess) return e;
+        g_occ_enc = occ > 0 ? occ : 1;
+    }
+    int64_t grid = (int64_t)sm_count * g_occ_enc;
+    if (grid > L.max_tiles) grid = L.max_tiles;
+    if (grid < 1) grid = 1;
+    char *base = static_cast<char *>(d_scratch);
+    b64enc_tiles<<<(unsigned)grid, kThreads, 0, stream>>>(
+        d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
+        reinterpret_cast<const int *>(base), d_in_off, n_units);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_b64dec(const char *d_in, const int64_t *d_in_off, int64_t n_units,
+                          int64_t total_in_bytes, uint8_t *d_out, const int64_t *d_out_off,
+                          int64_t *d_out_len, int64_t *d_status, void *d_scratch,
+                          size_t scratch_bytes, cudaStream_t stream, int sm_count) {
+    if (n_units <= 0) return cudaSuccess;
+    ScratchLayout L = scratch_layout(n_units, total_in_bytes, kDecTileIn);
+    if (scratch_bytes < L.total) return cudaErrorInvalidValue;
+    cudaError_t e = plan(d_in_off, d_out_off, n_units, kDecTileIn, 1, L, d_scratch, d_out_len,
+                         d_status, stream);
+    if (e != cudaSuccess) return e;
+    if (g_occ_dec == 0) {
+        int occ = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, b64dec_tiles, kThreads, 0);
+        if (e != cudaSuccess) return e;
+        g_occ_dec = occ > 0 ? occ : 1;
+    }
+    int64_t grid = (int64_t)sm_count * g_occ_dec;
+    if (grid > L.max_tiles) grid = L.max_tiles;
+    if (grid < 1) grid = 1;
+    char *base = static_cast<char *>(d_scratch);
+    b64dec_tiles<<<(unsigned)grid, kThreads, 0, stream>>>(
+        d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
+        reinterpret_cast<const int *>(base), d_in_off, n_units, d_out_len, d_status);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    int64_t sg = (n_units + 127) / 128;
+    if (sg > (int64_t)sm_count * 16) sg = (int64_t)sm_count * 16;
+    b64dec_slow<<<(unsigned)sg, 128, 0, stream>>>(d_in, d_in_off, n_units, d_out, d_out_off,
+                                                  d_out_len, d_status);
+    return cudaGetLastError();
+}
+
+}  // namespace kvedge

@@ -1,0 +1,50 @@
+// Internal launcher interface of the base64 kernels (C++ linkage; the C ABI lives in capi.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace kvedge {
+
+// Input bytes per encode tile: 4 rows of 256 threads x 12 bytes. A multiple of 12, so
+// every tile of a unit starts on a 3-byte group and its output on a 16-byte step.
+constexpr int kEncTileIn = 12288;
+constexpr int kEncTileOut = kEncTileIn / 3 * 4;
+// Input characters per decode tile: 4 rows of 256 threads x 16 characters.
+constexpr int kDecTileIn = 16384;
+constexpr int kThreads = 256;
+constexpr int kPlanBlock = 1024;  // units per block in the plan kernels
+
+// One tile of work: a contiguous piece of one unit.
+struct __align__(32) TileDesc {
+    int64_t in_pos;   // absolute byte offset in the input blob
+    int64_t out_pos;  // absolute byte offset in the output blob
+    int32_t len;      // input bytes in this tile (<= tile size)
+    int32_t unit;     // unit index
+    int32_t flags;    // bit0: last tile of its unit
+    int32_t pad;
+};
+
+// Scratch layout (device memory owned by the caller of the *_dev entry points):
+//   [0, 256)                 header: int32 n_tiles
+//   [256, 256 + 4*nb)        per-plan-block tile counts (nb = ceil(n_units / kPlanBlock))
+//   [desc_off, ...)          TileDesc[max_tiles]
+struct ScratchLayout {
+    size_t block_sums_off;
+    size_t desc_off;
+    size_t total;
+    int64_t max_tiles;
+    int64_t n_plan_blocks;
+};
+ScratchLayout scratch_layout(int64_t n_units, int64_t total_in_bytes, int tile_in);
+
+cudaError_t launch_b64enc(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
+                          int64_t total_in_bytes, char *d_out, const int64_t *d_out_off,
+                          void *d_scratch, size_t scratch_bytes, cudaStream_t stream, int sm_count);
+
+cudaError_t launch_b64dec(const char *d_in, const int64_t *d_in_off, int64_t n_units,
+                          int64_t total_in_bytes, uint8_t *d_out, const int64_t *d_out_off,
+                          int64_t *d_out_len, int64_t *d_status, void *d_scratch,
+                          size_t scratch_bytes, cudaStream_t stream, int sm_count);
+
+}  // namespace kvedge

@@ -1,0 +1,362 @@
+// extern "C" boundary of libkvedge_b200.so (declared in include/kvedge_b200.h).
+//
+// Two families:
+//   *_dev        device-resident packed batches, asynchronous on the caller's stream;
+//   host-buffer  what a template engine calls (Sprig `b64enc(string) string`, reference
+//                sites aziot-edge-runtime-config-secret.yaml:6 and
+//                aziot-edge-vm-cloud-init-secret.yaml:6): copies in, encodes on the GPU,
+//                copies out, chunked over three streams so H2D / kernel / D2H overlap.
+// There is no CPU implementation behind any of them.
+#include "../../include/kvedge_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "b64_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+    if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ||
+        e == cudaErrorInitializationError)
+        return fail(KV_ENODEVICE, "%s: %s (no CUDA device; this library has no CPU fallback)",
+                    what, cudaGetErrorString(e));
+    return fail(KV_ECUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+#define KV_CUDA(call)                                         \
+    do {                                                      \
+        cudaError_t e_ = (call);                              \
+        if (e_ != cudaSuccess) return cuda_fail(e_, #call);   \
+    } while (0)
+
+int g_sm_count[64];
+std::mutex g_mu;
+
+int sm_count_of_current_device(int *out) {
+    int dev = 0;
+    KV_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(KV_EINVAL, "device index %d out of range", dev);
+    if (g_sm_count[dev] == 0) {
+        int n = 0;
+        KV_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+        g_sm_count[dev] = n;
+    }
+    *out = g_sm_count[dev];
+    return KV_OK;
+}
+
+// ------------------------------------------------------------------ host-buffer pipeline
+constexpr int kSlots = 3;
+constexpr int64_t kChunkBytes = 32ll << 20;  // input bytes per pipeline chunk
+
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    bool busy = false;
+    char *d_in = nullptr;      size_t cap_in = 0;
+    char *d_out = nullptr;     size_t cap_out = 0;
+    int64_t *d_off = nullptr;  size_t cap_off = 0;   // in_off | out_off | out_len | status
+    char *d_scratch = nullptr; size_t cap_scratch = 0;
+    int64_t *h_off = nullptr;  size_t cap_hoff = 0;  // pinned mirror of d_off
+};
+
+struct HostCtx {
+    int device = 0;
+    bool ready = false;
+    Slot slot[kSlots];
+};
+HostCtx g_ctx;
+
+template <typename T>
+int grow(T **p, size_t *cap, size_t need) {
+    if (need <= *cap) return KV_OK;
+    if (*p) KV_CUDA(cudaFree(*p));
+    *p = nullptr;
+    *cap = 0;
+    size_t want = std::max(need, (size_t)1 << 20);
+    want = (want + (want >> 2) + 255) / 256 * 256;
+    void *q = nullptr;
+    cudaError_t e = cudaMalloc(&q, want);
+    if (e != cudaSuccess) return fail(KV_ENOMEM, "cudaMalloc(%zu): %s", want, cudaGetErrorString(e));
+    *p = static_cast<T *>(q);
+    *cap = want;
+    return KV_OK;
+}
+
+int grow_pinned(int64_t **p, size_t *cap, size_t need) {
+    if (need <= *cap) return KV_OK;
+    if (*p) KV_CUDA(cudaFreeHost(*p));
+    *p = nullptr;
+    *cap = 0;
+    size_t want = std::max(need, (size_t)1 << 16);
+    want = (want + (want >> 2) + 255) / 256 * 256;
+    void *q = nullptr;
+    cudaError_t e = cudaMallocHost(&q, want);
+    if (e != cudaSuccess) return fail(KV_ENOMEM, "cudaMallocHost(%zu): %s", want, cudaGetErrorString(e));
+    *p = static_cast<int64_t *>(q);
+    *cap = want;
+    return KV_OK;
+}
+
+int ctx_init() {
+    if (g_ctx.ready) return KV_OK;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+    if (n <= 0) return fail(KV_ENODEVICE, "no CUDA device (this library has no CPU fallback)");
+    KV_CUDA(cudaSetDevice(g_ctx.device));
+    for (int i = 0; i < kSlots; ++i) {
+        KV_CUDA(cudaStreamCreateWithFlags(&g_ctx.slot[i].stream, cudaStreamNonBlocking));
+        KV_CUDA(cudaEventCreateWithFlags(&g_ctx.slot[i].done, cudaEventDisableTiming));
+    }
+    g_ctx.ready = true;
+    return KV_OK;
+}
+
+int slot_wait(Slot &s) {
+    if (s.busy) {
+        KV_CUDA(cudaEventSynchronize(s.done));
+        s.busy = false;
+    }
+    return KV_OK;
+}
+
+// Run units [lo, hi) of a host packed batch through one slot. mode 0 = encode, 1 = decode.
+int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *out,
+              const int64_t *out_off, int64_t lo, int64_t hi, int64_t *out_len,
+              int64_t *status, int sm_count) {
+    int rc = slot_wait(s);
+    if (rc) return rc;
+    const int64_t n = hi - lo;
+    const int64_t ibeg = in_off[lo], iend = in_off[hi];
+    const int64_t obeg = out_off[lo], oend = out_off[hi];
+    const int64_t in_bytes = iend - ibeg, out_bytes = oend - obeg;
+    // keep each unit's alignment (mod 16) identical on the device and on the host side
+    const int64_t ishift = ibeg & 15, oshift = obeg & 15;
+    const int tile = mode == 0 ? kvedge::kEncTileIn : kvedge::kDecTileIn;
+    kvedge::ScratchLayout L = kvedge::scratch_layout(n, in_bytes + ishift, tile);
+    if ((rc = grow(&s.d_in, &s.cap_in, (size_t)(in_bytes + ishift + 32)))) return rc;
+    if ((rc = grow(&s.d_out, &s.cap_out, (size_t)(out_bytes + oshift + 32)))) return rc;
+    const size_t off_words = (size_t)(n + 1) * 2 + (mode ? (size_t)n * 2 : 0);
+    if ((rc = grow(&s.d_off, &s.cap_off, off_words * 8))) return rc;
+    if ((rc = grow_pinned(&s.h_off, &s.cap_hoff, off_words * 8))) return rc;
+    if ((rc = grow(&s.d_scratch, &s.cap_scratch, L.total))) return rc;
+    int64_t *h_in_off = s.h_off, *h_out_off = s.h_off + (n + 1);
+    for (int64_t k = 0; k <= n; ++k) {
+        h_in_off[k] = in_off[lo + k] - ibeg + ishift;
+        h_out_off[k] = out_off[lo + k] - obeg + oshift;
+    }
+    int64_t *d_in_off = s.d_off, *d_out_off = s.d_off + (n + 1);
+    int64_t *d_len = s.d_off + 2 * (n + 1), *d_status = d_len + n;
+    KV_CUDA(cudaMemcpyAsync(s.d_off, s.h_off, (size_t)(n + 1) * 16, cudaMemcpyHostToDevice, s.stream));
+    if (in_bytes > 0)
+        KV_CUDA(cudaMemcpyAsync(s.d_in + ishift, in + ibeg, (size_t)in_bytes, cudaMemcpyHostToDevice, s.stream));
+    cudaError_t e;
+    if (mode == 0)
+        e = kvedge::launch_b64enc(reinterpret_cast<const uint8_t *>(s.d_in), d_in_off, n,
+                                  in_bytes + ishift, s.d_out, d_out_off, s.d_scratch,
+                                  s.cap_scratch, s.stream, sm_count);
+    else
+        e = kvedge::launch_b64dec(s.d_in, d_in_off, n, in_bytes + ishift,
+                                  reinterpret_cast<uint8_t *>(s.d_out), d_out_off, d_len, d_status,
+                                  s.d_scratch, s.cap_scratch, s.stream, sm_count);
+    if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+    if (out_bytes > 0)
+        KV_CUDA(cudaMemcpyAsync(out + obeg, s.d_out + oshift, (size_t)out_bytes, cudaMemcpyDeviceToHost, s.stream));
+    if (mode == 1) {
+        KV_CUDA(cudaMemcpyAsync(out_len + lo, d_len, (size_t)n * 8, cudaMemcpyDeviceToHost, s.stream));
+        KV_CUDA(cudaMemcpyAsync(status + lo, d_status, (size_t)n * 8, cudaMemcpyDeviceToHost, s.stream));
+    }
+    KV_CUDA(cudaEventRecord(s.done, s.stream));
+    s.busy = true;
+    return KV_OK;
+}
+
+int run_host_batch(int mode, const char *in, const int64_t *in_off, int64_t n_units, char *out,
+                   const int64_t *out_off, int64_t *out_len, int64_t *status) {
+    if (n_units < 0) return fail(KV_EINVAL, "n_units < 0");
+    if (n_units == 0) return KV_OK;
+    if (!in_off || !out_off) return fail(KV_EINVAL, "null offsets");
+    for (int64_t i = 0; i < n_units; ++i) {
+        const int64_t len = in_off[i + 1] - in_off[i];
+        if (len < 0) return fail(KV_EINVAL, "in_off is not non-decreasing at unit %lld", (long long)i);
+        const int64_t need = mode == 0 ? (int64_t)kv_b64enc_len((size_t)len)
+                                       : (int64_t)kv_b64dec_maxlen((size_t)len);
+        if (out_off[i + 1] - out_off[i] < need)
+            return fail(KV_EINVAL, "unit %lld: output capacity %lld < %lld", (long long)i,
+                        (long long)(out_off[i + 1] - out_off[i]), (long long)need);
+    }
+    if (in_off[n_units] > in_off[0] && !in) return fail(KV_EINVAL, "null input");
+    if (out_off[n_units] > out_off[0] && !out) return fail(KV_EINVAL, "null output");
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ctx_init();
+    if (rc) return rc;
+    KV_CUDA(cudaSetDevice(g_ctx.device));
+    int sms = 0;
+    if ((rc = sm_count_of_current_device(&sms))) return rc;
+    int64_t lo = 0;
+    int turn = 0;
+    while (lo < n_units) {
+        int64_t hi = lo + 1;
+        while (hi < n_units && in_off[hi + 1] - in_off[lo] <= kChunkBytes) ++hi;
+        rc = run_chunk(g_ctx.slot[turn % kSlots], mode, in, in_off, out, out_off, lo, hi, out_len,
+                       status, sms);
+        if (rc) break;
+        lo = hi;
+        ++turn;
+    }
+    for (int i = 0; i < kSlots; ++i) {
+        int r2 = slot_wait(g_ctx.slot[i]);
+        if (!rc) rc = r2;
+    }
+    return rc;
+}
+
+}  // namespace
+
+extern "C" {
+
+int kv_version(void) { return 100; }
+
+const char *kv_last_error(void) { return g_err.c_str(); }
+
+int kv_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+size_t kv_b64enc_len(size_t n) { return (n + 2) / 3 * 4; }
+size_t kv_b64dec_maxlen(size_t n) { return n / 4 * 3; }
+
+size_t kv_b64_scratch_bytes(int64_t n_units, int64_t total_in_bytes) {
+    // the encode tile is the smaller one, so its table is the larger of the two
+    return kvedge::scratch_layout(n_units, total_in_bytes, kvedge::kEncTileIn).total;
+}
+
+int kv_b64enc_batch_dev(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
+                        int64_t total_in_bytes, char *d_out, const int64_t *d_out_off,
+                        void *d_scratch, size_t scratch_bytes, void *stream) {
+    if (n_units < 0 || total_in_bytes < 0) return fail(KV_EINVAL, "negative size");
+    if (n_units == 0) return KV_OK;
+    if (!d_in_off || !d_out_off || !d_scratch) return fail(KV_EINVAL, "null pointer");
+    size_t need = kvedge::scratch_layout(n_units, total_in_bytes, kvedge::kEncTileIn).total;
+    if (scratch_bytes < need)
+        return fail(KV_ENOMEM, "scratch too small: %zu < %zu (kv_b64_scratch_bytes)", scratch_bytes, need);
+    int sms = 0;
+    int rc = sm_count_of_current_device(&sms);
+    if (rc) return rc;
+    cudaError_t e = kvedge::launch_b64enc(d_in, d_in_off, n_units, total_in_bytes, d_out, d_out_off,
+                                          d_scratch, scratch_bytes, static_cast<cudaStream_t>(stream), sms);
+    if (e != cudaSuccess) return cuda_fail(e, "b64enc launch");
+    return KV_OK;
+}
+
+int kv_b64dec_batch_dev(const char *d_in, const int64_t *d_in_off, int64_t n_units,
+                        int64_t total_in_bytes, uint8_t *d_out, const int64_t *d_out_off,
+                        int64_t *d_out_len, int64_t *d_status, void *d_scratch,
+                        size_t scratch_bytes, void *stream) {
+    if (n_units < 0 || total_in_bytes < 0) return fail(KV_EINVAL, "negative size");
+    if (n_units == 0) return KV_OK;
+    if (!d_in_off || !d_out_off || !d_scratch || !d_out_len || !d_status)
+        return fail(KV_EINVAL, "null pointer");
+    size_t need = kvedge::scratch_layout(n_units, total_in_bytes, kvedge::kDecTileIn).total;
+    if (scratch_bytes < need)
+        return fail(KV_ENOMEM, "scratch too small: %zu < %zu (kv_b64_scratch_bytes)", scratch_bytes, need);
+    int sms = 0;
+    int rc = sm_count_of_current_device(&sms);
+    if (rc) return rc;
+    cudaError_t e = kvedge::launch_b64dec(d_in, d_in_off, n_units, total_in_bytes, d_out, d_out_off,
+                                          d_out_len, d_status, d_scratch, scratch_bytes,
+                                          static_cast<cudaStream_t>(stream), sms);
+    if (e != cudaSuccess) return cuda_fail(e, "b64dec launch");
+    return KV_OK;
+}
+
+int kv_b64enc_batch(const uint8_t *in, const int64_t *in_off, int64_t n_units, char *out,
+                    const int64_t *out_off) {
+    return run_host_batch(0, reinterpret_cast<const char *>(in), in_off, n_units, out, out_off,
+                          nullptr, nullptr);
+}
+
+int kv_b64enc(const uint8_t *in, size_t n, char *out) {
+    if (n == 0) return KV_OK;
+    const int64_t io[2] = {0, (int64_t)n};
+    const int64_t oo[2] = {0, (int64_t)kv_b64enc_len(n)};
+    return kv_b64enc_batch(in, io, 1, out, oo);
+}
+
+int kv_b64dec_batch(const char *in, const int64_t *in_off, int64_t n_units, uint8_t *out,
+                    const int64_t *out_off, int64_t *out_len, int64_t *status) {
+    if (n_units > 0 && (!out_len || !status)) return fail(KV_EINVAL, "null out_len/status");
+    return run_host_batch(1, in, in_off, n_units, reinterpret_cast<char *>(out), out_off, out_len,
+                          status);
+}
+
+int kv_b64dec(const char *in, size_t n, uint8_t *out, size_t *out_n, size_t *err_off) {
+    if (out_n) *out_n = 0;
+    if (n == 0) return KV_OK;
+    const int64_t io[2] = {0, (int64_t)n};
+    const int64_t oo[2] = {0, (int64_t)kv_b64dec_maxlen(n)};
+    int64_t len = 0, st = -1;
+    int rc = kv_b64dec_batch(in, io, 1, out, oo, &len, &st);
+    if (rc) return rc;
+    if (out_n) *out_n = (size_t)len;
+    if (st >= 0) {
+        if (err_off) *err_off = (size_t)st;
+        return fail(KV_ECORRUPT, "illegal base64 data at input byte %lld", (long long)st);
+    }
+    return KV_OK;
+}
+
+int kv_set_device(int device) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (g_ctx.ready && device != g_ctx.device)
+        return fail(KV_EINVAL, "kv_set_device after first use; call kv_shutdown() first");
+    g_ctx.device = device;
+    return KV_OK;
+}
+
+void kv_shutdown(void) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_ctx.ready) return;
+    cudaSetDevice(g_ctx.device);
+    for (int i = 0; i < kSlots; ++i) {
+        Slot &s = g_ctx.slot[i];
+        if (s.busy) cudaEventSynchronize(s.done);
+        if (s.d_in) cudaFree(s.d_in);
+        if (s.d_out) cudaFree(s.d_out);
+        if (s.d_off) cudaFree(s.d_off);
+        if (s.d_scratch) cudaFree(s.d_scratch);
+        if (s.h_off) cudaFreeHost(s.h_off);
+        if (s.done) cudaEventDestroy(s.done);
+        if (s.stream) cudaStreamDestroy(s.stream);
+        s = Slot();
+    }
+    g_ctx.ready = false;
+}
+
+}  // extern "C"

@@ -1,0 +1,152 @@
+"""ctypes front-end of the CPU checker in ``b64_ref.c``.
+
+TEST INFRASTRUCTURE ONLY: imported by ``tests/``, ``__graft_entry__.smoke()``
+and ``bench.py``'s ``cpu_baseline`` / ``--impl reference`` legs, never by
+``kvedge_b200`` (the product path has no CPU fallback).
+
+Follows the reference call sites
+``deployment/helm/templates/aziot-edge-runtime-config-secret.yaml:6`` and
+``deployment/helm/templates/aziot-edge-vm-cloud-init-secret.yaml:6`` (Sprig
+``b64enc`` -> Go ``encoding/base64.StdEncoding``; third-party, not vendored in
+the reference, version unpinned).  Parity unpinned by the reference's own
+artefacts; pinned to RFC 4648 vectors, coreutils and binascii in
+``tests/test_oracle_b64.py``.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "liboracle_b64.so")
+_lib = None
+
+
+def build(force: bool = False) -> str:
+    """Compile ``b64_ref.c`` with gcc (``make -C oracle``)."""
+    src = os.path.join(_HERE, "b64_ref.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle_b64.so"],
+                              stdout=subprocess.DEVNULL)
+    return _SO
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        L = ctypes.CDLL(_SO)
+        c = ctypes
+        L.oracle_b64_encoded_len.restype = c.c_size_t
+        L.oracle_b64_encoded_len.argtypes = [c.c_size_t]
+        L.oracle_b64_encode.restype = c.c_size_t
+        L.oracle_b64_encode.argtypes = [c.c_void_p, c.c_size_t, c.c_void_p]
+        L.oracle_b64_decode.restype = c.c_int
+        L.oracle_b64_decode.argtypes = [c.c_void_p, c.c_size_t, c.c_void_p,
+                                        c.POINTER(c.c_size_t), c.POINTER(c.c_size_t)]
+        L.oracle_b64_encode_batch.restype = None
+        L.oracle_b64_encode_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int64,
+                                              c.c_void_p, c.c_void_p]
+        L.oracle_b64_decode_batch.restype = None
+        L.oracle_b64_decode_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int64, c.c_void_p,
+                                              c.c_void_p, c.c_void_p, c.c_void_p]
+        _lib = L
+    return _lib
+
+
+def encoded_len(n: int) -> int:
+    return (n + 2) // 3 * 4
+
+
+def encode(data: bytes) -> bytes:
+    """Go ``base64.StdEncoding.EncodeToString`` of ``data``."""
+    data = bytes(data)
+    out = ctypes.create_string_buffer(encoded_len(len(data)) or 1)
+    n = lib().oracle_b64_encode(data, len(data), out)
+    return out.raw[:n]
+
+
+class CorruptInputError(ValueError):
+    """Go ``base64.CorruptInputError``; ``offset`` is the offending input byte."""
+
+    def __init__(self, offset: int, partial: bytes = b""):
+        super().__init__(f"illegal base64 data at input byte {offset}")
+        self.offset = offset
+        self.partial = partial
+
+
+def decode(data: bytes) -> bytes:
+    """Go ``base64.StdEncoding.DecodeString`` of ``data`` (raises on corrupt input)."""
+    data = bytes(data)
+    out = ctypes.create_string_buffer(len(data) // 4 * 3 + 4)
+    n = ctypes.c_size_t(0)
+    eo = ctypes.c_size_t(0)
+    rc = lib().oracle_b64_decode(data, len(data), out, ctypes.byref(n), ctypes.byref(eo))
+    if rc:
+        raise CorruptInputError(eo.value, out.raw[:n.value])
+    return out.raw[:n.value]
+
+
+def encode_offsets(in_off: np.ndarray, align: int = 1) -> np.ndarray:
+    """Output offsets (n+1) of a packed batch: unit i holds 4*ceil(len_i/3) chars,
+    each unit start rounded up to ``align`` bytes."""
+    lens = np.diff(in_off.astype(np.int64))
+    olen = (lens + 2) // 3 * 4
+    if align > 1:
+        olen = (olen + align - 1) // align * align
+    out = np.zeros(len(lens) + 1, dtype=np.int64)
+    np.cumsum(olen, out=out[1:])
+    return out
+
+
+def encode_batch(blob: np.ndarray, in_off: np.ndarray, out_off: np.ndarray | None = None,
+                 threads: int = 1, out: np.ndarray | None = None) -> np.ndarray:
+    """Encode every unit of a packed batch; returns the packed output blob (uint8)."""
+    blob = np.ascontiguousarray(blob, dtype=np.uint8)
+    in_off = np.ascontiguousarray(in_off, dtype=np.int64)
+    n = len(in_off) - 1
+    if out_off is None:
+        out_off = encode_offsets(in_off)
+    out_off = np.ascontiguousarray(out_off, dtype=np.int64)
+    assert len(out_off) == n + 1, "out_off holds n+1 entries (last = total capacity)"
+    total = int(out_off[-1])
+    if out is None:
+        out = np.zeros(max(total, 1), dtype=np.uint8)
+    L = lib()
+    if threads <= 1 or n < 2 * threads:
+        L.oracle_b64_encode_batch(blob.ctypes.data, in_off.ctypes.data, n,
+                                  out.ctypes.data, out_off.ctypes.data)
+    else:
+        bounds = np.linspace(0, n, threads + 1).astype(np.int64)
+
+        def work(k):
+            lo, hi = int(bounds[k]), int(bounds[k + 1])
+            if hi > lo:
+                L.oracle_b64_encode_batch(blob.ctypes.data, in_off[lo:].ctypes.data, hi - lo,
+                                          out.ctypes.data, out_off[lo:].ctypes.data)
+
+        with ThreadPoolExecutor(threads) as ex:
+            list(ex.map(work, range(threads)))
+    return out[:total]
+
+
+def decode_batch(blob: np.ndarray, in_off: np.ndarray, out_off: np.ndarray):
+    """Decode every unit; returns (out blob, out_len[n], status[n]) with status -1 = ok,
+    else Go's CorruptInputError offset."""
+    blob = np.ascontiguousarray(blob, dtype=np.uint8)
+    in_off = np.ascontiguousarray(in_off, dtype=np.int64)
+    out_off = np.ascontiguousarray(out_off, dtype=np.int64)
+    n = len(in_off) - 1
+    assert len(out_off) == n + 1
+    cap = int(out_off[-1])
+    out = np.zeros(max(cap, 1) + 4, dtype=np.uint8)
+    out_len = np.zeros(max(n, 1), dtype=np.int64)
+    status = np.zeros(max(n, 1), dtype=np.int64)
+    lib().oracle_b64_decode_batch(blob.ctypes.data, in_off.ctypes.data, n, out.ctypes.data,
+                                  out_off.ctypes.data, out_len.ctypes.data, status.ctypes.data)
+    return out[:cap], out_len[:n], status[:n]
