@@ -68,6 +68,16 @@ int kv_b64enc_batch_dev(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_
                         int64_t total_in_bytes, char *d_out, const int64_t *d_out_off,
                         void *d_scratch, size_t scratch_bytes, void *stream);
 
+/* The same call split in two, for callers that re-encode new bytes under unchanged offsets
+ * (same fleet, new configs): kv_b64enc_plan_dev builds the tile table in d_scratch from the
+ * offsets, kv_b64enc_run_dev runs the encode kernel over it.  plan + run == batch_dev.   */
+int kv_b64enc_plan_dev(const int64_t *d_in_off, int64_t n_units, int64_t total_in_bytes,
+                       const int64_t *d_out_off, void *d_scratch, size_t scratch_bytes,
+                       void *stream);
+int kv_b64enc_run_dev(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
+                      int64_t total_in_bytes, char *d_out, const void *d_scratch,
+                      size_t scratch_bytes, void *stream);
+
 /* Inverse of the above: what the Kubernetes API server / KubeVirt do to
  * Secret.data.userdata before exposing it as the `userdata` file consumed at
  * deployment/helm/templates/_helper.tpl:64,73 (via aziot-edge-vm.yaml:25-28,49-51).

@@ -23,6 +23,10 @@ SIGNATURES = {
     "kv_b64_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64]),
     "kv_b64enc_batch_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "kv_b64enc_plan_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
+                                     C.c_size_t, C.c_void_p]),
+    "kv_b64enc_run_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
+                                    C.c_void_p, C.c_size_t, C.c_void_p]),
     "kv_b64dec_batch_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                                       C.c_void_p]),

@@ -158,6 +158,23 @@ def b64enc_device(d_in, d_in_off, d_out, d_out_off, d_scratch, total_in_bytes: O
                                          _stream_handle(stream)))
 
 
+def b64enc_plan_device(d_in_off, d_out_off, d_scratch, total_in_bytes: int, stream=None) -> None:
+    """Build the tile table for a packed batch (reusable while the offsets do not change)."""
+    n = d_in_off.numel() - 1
+    check(_lib.lib().kv_b64enc_plan_dev(d_in_off.data_ptr(), n, total_in_bytes, d_out_off.data_ptr(),
+                                        d_scratch.data_ptr(), d_scratch.numel() * d_scratch.element_size(),
+                                        _stream_handle(stream)))
+
+
+def b64enc_run_device(d_in, d_in_off, d_out, d_scratch, total_in_bytes: int, stream=None) -> None:
+    """Run the encode kernel over a tile table built by ``b64enc_plan_device``."""
+    n = d_in_off.numel() - 1
+    check(_lib.lib().kv_b64enc_run_dev(d_in.data_ptr(), d_in_off.data_ptr(), n, total_in_bytes,
+                                       d_out.data_ptr(), d_scratch.data_ptr(),
+                                       d_scratch.numel() * d_scratch.element_size(),
+                                       _stream_handle(stream)))
+
+
 def b64dec_device(d_in, d_in_off, d_out, d_out_off, d_out_len, d_status, d_scratch,
                   total_in_bytes: Optional[int] = None, stream=None) -> None:
     """Decode a packed batch resident in HBM. Asynchronous on ``stream``."""
@@ -172,5 +189,5 @@ def b64dec_device(d_in, d_in_off, d_out, d_out_off, d_out_len, d_status, d_scrat
 
 
 __all__ = ["b64enc", "b64dec", "b64enc_many", "b64dec_many", "b64enc_packed", "b64dec_packed",
-           "b64enc_device", "b64dec_device", "scratch_bytes", "encode_offsets", "decode_offsets",
+           "b64enc_device", "b64dec_device", "b64enc_plan_device", "b64enc_run_device", "scratch_bytes", "encode_offsets", "decode_offsets",
            "encoded_len", "CorruptInputError", "KvError"]

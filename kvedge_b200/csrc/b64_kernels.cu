@@ -450,16 +450,22 @@ static cudaError_t plan(const int64_t *d_in_off, const int64_t *d_out_off, int64
     return cudaGetLastError();
 }
 
-cudaError_t launch_b64enc(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
-                          int64_t total_in_bytes, char *d_out, const int64_t *d_out_off,
-                          void *d_scratch, size_t scratch_bytes, cudaStream_t stream,
-                          int sm_count) {
+cudaError_t launch_b64enc_plan(const int64_t *d_in_off, int64_t n_units, int64_t total_in_bytes,
+                               const int64_t *d_out_off, void *d_scratch, size_t scratch_bytes,
+                               cudaStream_t stream) {
     if (n_units <= 0) return cudaSuccess;
     ScratchLayout L = scratch_layout(n_units, total_in_bytes, kEncTileIn);
     if (scratch_bytes < L.total) return cudaErrorInvalidValue;
-    cudaError_t e = plan(d_in_off, d_out_off, n_units, kEncTileIn, 0, L, d_scratch, nullptr,
-                         nullptr, stream);
-    if (e != cudaSuccess) return e;
+    return plan(d_in_off, d_out_off, n_units, kEncTileIn, 0, L, d_scratch, nullptr, nullptr, stream);
+}
+
+cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
+                              int64_t total_in_bytes, char *d_out, const void *d_scratch,
+                              size_t scratch_bytes, cudaStream_t stream, int sm_count) {
+    if (n_units <= 0) return cudaSuccess;
+    ScratchLayout L = scratch_layout(n_units, total_in_bytes, kEncTileIn);
+    if (scratch_bytes < L.total) return cudaErrorInvalidValue;
+    cudaError_t e;
     if (g_occ_enc == 0) {
         int occ = 0;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, b64enc_tiles, kThreads, 0);
@@ -469,11 +475,22 @@ cudaError_t launch_b64enc(const uint8_t *d_in, const int64_t *d_in_off, int64_t 
     int64_t grid = (int64_t)sm_count * g_occ_enc;
     if (grid > L.max_tiles) grid = L.max_tiles;
     if (grid < 1) grid = 1;
-    char *base = static_cast<char *>(d_scratch);
+    const char *base = static_cast<const char *>(d_scratch);
     b64enc_tiles<<<(unsigned)grid, kThreads, 0, stream>>>(
         d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
         reinterpret_cast<const int *>(base), d_in_off, n_units);
     return cudaGetLastError();
+}
+
+cudaError_t launch_b64enc(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
+                          int64_t total_in_bytes, char *d_out, const int64_t *d_out_off,
+                          void *d_scratch, size_t scratch_bytes, cudaStream_t stream,
+                          int sm_count) {
+    cudaError_t e = launch_b64enc_plan(d_in_off, n_units, total_in_bytes, d_out_off, d_scratch,
+                                       scratch_bytes, stream);
+    if (e != cudaSuccess) return e;
+    return launch_b64enc_run(d_in, d_in_off, n_units, total_in_bytes, d_out, d_scratch,
+                             scratch_bytes, stream, sm_count);
 }
 
 cudaError_t launch_b64dec(const char *d_in, const int64_t *d_in_off, int64_t n_units,

@@ -42,6 +42,15 @@ cudaError_t launch_b64enc(const uint8_t *d_in, const int64_t *d_in_off, int64_t 
                           int64_t total_in_bytes, char *d_out, const int64_t *d_out_off,
                           void *d_scratch, size_t scratch_bytes, cudaStream_t stream, int sm_count);
 
+// The two halves of launch_b64enc: build the tile table once, run it many times (same
+// offsets, new bytes).
+cudaError_t launch_b64enc_plan(const int64_t *d_in_off, int64_t n_units, int64_t total_in_bytes,
+                               const int64_t *d_out_off, void *d_scratch, size_t scratch_bytes,
+                               cudaStream_t stream);
+cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
+                              int64_t total_in_bytes, char *d_out, const void *d_scratch,
+                              size_t scratch_bytes, cudaStream_t stream, int sm_count);
+
 cudaError_t launch_b64dec(const char *d_in, const int64_t *d_in_off, int64_t n_units,
                           int64_t total_in_bytes, uint8_t *d_out, const int64_t *d_out_off,
                           int64_t *d_out_len, int64_t *d_status, void *d_scratch,

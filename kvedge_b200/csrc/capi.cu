@@ -275,6 +275,39 @@ int kv_b64enc_batch_dev(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_
     return KV_OK;
 }
 
+int kv_b64enc_plan_dev(const int64_t *d_in_off, int64_t n_units, int64_t total_in_bytes,
+                       const int64_t *d_out_off, void *d_scratch, size_t scratch_bytes,
+                       void *stream) {
+    if (n_units < 0 || total_in_bytes < 0) return fail(KV_EINVAL, "negative size");
+    if (n_units == 0) return KV_OK;
+    if (!d_in_off || !d_out_off || !d_scratch) return fail(KV_EINVAL, "null pointer");
+    size_t need = kvedge::scratch_layout(n_units, total_in_bytes, kvedge::kEncTileIn).total;
+    if (scratch_bytes < need)
+        return fail(KV_ENOMEM, "scratch too small: %zu < %zu (kv_b64_scratch_bytes)", scratch_bytes, need);
+    cudaError_t e = kvedge::launch_b64enc_plan(d_in_off, n_units, total_in_bytes, d_out_off, d_scratch,
+                                               scratch_bytes, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "b64enc plan launch");
+    return KV_OK;
+}
+
+int kv_b64enc_run_dev(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
+                      int64_t total_in_bytes, char *d_out, const void *d_scratch,
+                      size_t scratch_bytes, void *stream) {
+    if (n_units < 0 || total_in_bytes < 0) return fail(KV_EINVAL, "negative size");
+    if (n_units == 0) return KV_OK;
+    if (!d_in_off || !d_scratch) return fail(KV_EINVAL, "null pointer");
+    size_t need = kvedge::scratch_layout(n_units, total_in_bytes, kvedge::kEncTileIn).total;
+    if (scratch_bytes < need)
+        return fail(KV_ENOMEM, "scratch too small: %zu < %zu (kv_b64_scratch_bytes)", scratch_bytes, need);
+    int sms = 0;
+    int rc = sm_count_of_current_device(&sms);
+    if (rc) return rc;
+    cudaError_t e = kvedge::launch_b64enc_run(d_in, d_in_off, n_units, total_in_bytes, d_out, d_scratch,
+                                              scratch_bytes, static_cast<cudaStream_t>(stream), sms);
+    if (e != cudaSuccess) return cuda_fail(e, "b64enc run launch");
+    return KV_OK;
+}
+
 int kv_b64dec_batch_dev(const char *d_in, const int64_t *d_in_off, int64_t n_units,
                         int64_t total_in_bytes, uint8_t *d_out, const int64_t *d_out_off,
                         int64_t *d_out_len, int64_t *d_status, void *d_scratch,

@@ -1,0 +1,62 @@
+"""The C-ABI library loads without a GPU, exports every symbol include/kvedge_b200.h
+declares, and refuses to compute without a device (no CPU fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from kvedge_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    names = set()
+    for fn in os.listdir(os.path.join(ROOT, "include")):
+        if fn.endswith(".h"):
+            text = open(os.path.join(ROOT, "include", fn)).read()
+            text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+            names |= set(re.findall(r"\b(kv_[a-z0-9_]+)\s*\(", text))
+    return names
+
+
+def test_header_and_binding_table_agree():
+    assert _declared_symbols() == set(_lib.SIGNATURES)
+
+
+def test_library_exports_every_declared_symbol():
+    L = ctypes.CDLL(_lib.LIB_PATH)
+    for name in sorted(_declared_symbols()):
+        assert getattr(L, name) is not None, name
+
+
+def test_size_helpers_need_no_device():
+    L = _lib.lib()
+    assert L.kv_version() >= 100
+    assert [L.kv_b64enc_len(n) for n in (0, 1, 2, 3, 4, 2006)] == [0, 4, 4, 4, 8, 2676]
+    assert [L.kv_b64dec_maxlen(n) for n in (0, 3, 4, 2676)] == [0, 0, 3, 2007]
+    assert L.kv_b64_scratch_bytes(1, 12) >= 256
+
+
+def test_no_cpu_fallback_without_a_device():
+    L = _lib.lib()
+    if L.kv_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    out = ctypes.create_string_buffer(8)
+    assert L.kv_b64enc(b"foo", 3, out) == _lib.KV_ENODEVICE
+    assert b"no CPU fallback" in L.kv_last_error()
+    assert out.raw == b"\0" * 8
+    from kvedge_b200 import b64
+    with pytest.raises(_lib.KvError):
+        b64.b64enc(b"foo")
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "kvedge_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")):
+                text = open(os.path.join(dirpath, fn), errors="replace").read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), fn
+                assert "liboracle" not in text and "b64_ref" not in text, fn

@@ -1,0 +1,200 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the CPU checker (oracle/)
+and the committed golden vectors. Bit-exact: this is byte work, there is no tolerance."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from kvedge_b200 import b64, workload
+from oracle import b64 as ob64
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    from kvedge_b200 import _lib
+    assert _lib.lib().kv_device_count() > 0
+    return torch
+
+
+def _dev_encode(torch, units, out_align=16, in_shift=0, out_shift=0):
+    """Encode through kv_b64enc_batch_dev; returns list of per-unit outputs."""
+    blob, in_off = workload.pack(units)
+    in_off = in_off + in_shift
+    out_off = b64.encode_offsets(in_off, align=out_align) + out_shift
+    d_in = torch.zeros(int(in_off[-1]) + 64, dtype=torch.uint8, device="cuda")
+    d_in[in_shift:in_shift + len(blob)] = torch.from_numpy(blob).cuda()
+    d_in_off = torch.from_numpy(in_off).cuda()
+    d_out_off = torch.from_numpy(out_off).cuda()
+    d_out = torch.full((int(out_off[-1]) + 64,), 0x7E, dtype=torch.uint8, device="cuda")
+    scratch = torch.empty(b64.scratch_bytes(len(units), int(in_off[-1])), dtype=torch.uint8, device="cuda")
+    b64.b64enc_device(d_in, d_in_off, d_out, d_out_off, scratch, total_in_bytes=int(in_off[-1]))
+    torch.cuda.synchronize()
+    raw = d_out.cpu().numpy().tobytes()
+    outs = [raw[int(out_off[i]):int(out_off[i]) + b64.encoded_len(len(u))] for i, u in enumerate(units)]
+    return outs, raw, out_off
+
+
+def test_rfc_and_golden_vectors_host_api(torch_cuda, golden_vectors):
+    for raw, enc in workload.RFC4648_VECTORS:
+        assert b64.b64enc(raw) == enc
+        assert b64.b64dec(enc) == raw
+    units = [bytes.fromhex(v["in_hex"]) for v in golden_vectors["encode"]]
+    got = b64.b64enc_many(units)
+    for v, g in zip(golden_vectors["encode"], got):
+        assert g == v["b64"].encode(), v["name"]
+    assert b64.b64dec_many(got) == units
+
+
+def test_named_inputs_f0_f8(torch_cuda, golden_vectors):
+    named = workload.named_inputs(0)
+    keys = sorted(named)
+    got = b64.b64enc_many([named[k] for k in keys])
+    for k, g in zip(keys, got):
+        meta = golden_vectors["named"][k]
+        assert len(g) == meta["b64_len"] and hashlib.sha256(g).hexdigest() == meta["b64_sha256"], k
+        assert g == ob64.encode(named[k])
+    assert b64.b64dec_many(got) == [named[k] for k in keys]
+
+
+def test_default_cloudinit_payload_fingerprint(torch_cuda, golden_chart):
+    """The a2 site on its real input: decode the golden Secret value, re-encode on the GPU."""
+    text = golden_chart["config1"]["cloudinit_default_b64"].encode()
+    payload = b64.b64dec(text)
+    assert len(payload) == 2006
+    assert hashlib.sha256(payload).hexdigest() == golden_chart["config1"]["cloudinit_default_payload_sha256"]
+    assert b64.b64enc(payload) == text
+
+
+@pytest.mark.parametrize("out_align", [16, 4, 1])
+@pytest.mark.parametrize("in_shift,out_shift", [(0, 0), (1, 0), (2, 4), (3, 5), (0, 7)])
+def test_device_encode_all_alignments(torch_cuda, out_align, in_shift, out_shift):
+    rng = np.random.default_rng(10 * in_shift + out_shift + out_align)
+    lens = list(range(0, 40)) + [3071, 3072, 3073, 12287, 12288, 12289, 12300, 24576, 24577, 40000]
+    units = [rng.bytes(n) for n in lens]
+    outs, raw, out_off = _dev_encode(torch_cuda, units, out_align, in_shift, out_shift)
+    for u, o in zip(units, outs):
+        assert o == ob64.encode(u), len(u)
+    # nothing written outside the units' own ranges
+    mask = np.ones(len(raw), dtype=bool)
+    for i, u in enumerate(units):
+        mask[int(out_off[i]):int(out_off[i]) + b64.encoded_len(len(u))] = False
+    assert (np.frombuffer(raw, np.uint8)[mask] == 0x7E).all()
+
+
+def test_device_encode_ragged_fleet_vs_oracle(torch_cuda):
+    """Mixed 11 KiB configs and 2.4 KB cloud-init payloads, like one fleet batch."""
+    rng = np.random.default_rng(5)
+    units = []
+    for i in range(300):
+        units.append(workload.config_toml(i % 7))
+        units.append(b"#cloud-config\n" + rng.bytes(2382))
+    outs, _, _ = _dev_encode(torch_cuda, units)
+    blob, off = workload.pack(units)
+    ref = ob64.encode_batch(blob, off, ob64.encode_offsets(off)).tobytes()
+    assert b"".join(outs) == ref
+
+
+def test_every_sextet_maps_to_the_alphabet(torch_cuda):
+    # all 64 sextet values in all four positions of a group
+    raw = bytes.fromhex("00108310518720928b30d38f41149351559761969b71d79f8218a39259a7a29aabb2dbafc31cb3d35db7e39ebbf3dfbf")
+    assert b64.b64enc(raw) == b"ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/"
+    rot = raw[1:] + raw[:1]
+    assert b64.b64enc(rot) == ob64.encode(rot)
+
+
+def test_decode_error_offsets_match_go(torch_cuda, golden_vectors):
+    for c in golden_vectors["decode"]:
+        text = bytes.fromhex(c["text_hex"])
+        if c["ok"]:
+            assert b64.b64dec(text) == bytes.fromhex(c["out_hex"]), text
+        else:
+            with pytest.raises(b64.CorruptInputError) as ei:
+                b64.b64dec(text)
+            assert ei.value.offset == c["offset"], text
+
+
+def test_decode_batch_mixed_clean_and_corrupt(torch_cuda):
+    rng = np.random.default_rng(11)
+    units, expect = [], []
+    for i in range(400):
+        raw = rng.bytes(int(rng.integers(0, 30000)))
+        enc = bytearray(ob64.encode(raw))
+        kind = i % 5
+        if kind == 1 and len(enc) > 8:
+            enc[int(rng.integers(0, len(enc) - 4))] = ord("*")
+        elif kind == 2 and len(enc) > 8:
+            p = int(rng.integers(1, len(enc)))
+            enc[p:p] = b"\r\n"
+        elif kind == 3 and len(enc) > 8:
+            del enc[-1]
+        units.append(bytes(enc))
+    blob, off = workload.pack(units)
+    dec_off = b64.decode_offsets(off)
+    out, _, out_len, status = b64.b64dec_packed(blob, off, dec_off)
+    ref_out, ref_len, ref_status = ob64.decode_batch(blob, off, dec_off)
+    assert np.array_equal(status, ref_status)
+    assert np.array_equal(out_len, ref_len)
+    for i in range(len(units)):
+        if ref_status[i] == -1:
+            a = out[int(dec_off[i]):int(dec_off[i]) + int(out_len[i])]
+            b = ref_out[int(dec_off[i]):int(dec_off[i]) + int(ref_len[i])]
+            assert np.array_equal(a, b), i
+
+
+def test_round_trip_at_bench_scale(torch_cuda):
+    """Size-independent property at a fleet-sized batch: encode -> decode is the identity,
+    every output byte is in the alphabet, and a checksum of the input survives."""
+    torch = torch_cuda
+    n, unit = 4096, 12 * 1024 + 1
+    g = torch.Generator(device="cuda").manual_seed(0)
+    d_in = torch.randint(0, 256, (n * unit,), dtype=torch.uint8, device="cuda", generator=g)
+    in_off = np.arange(n + 1, dtype=np.int64) * unit
+    out_off = b64.encode_offsets(in_off)
+    d_in_off, d_out_off = torch.from_numpy(in_off).cuda(), torch.from_numpy(out_off).cuda()
+    d_out = torch.zeros(int(out_off[-1]), dtype=torch.uint8, device="cuda")
+    scratch = torch.empty(b64.scratch_bytes(n, n * unit), dtype=torch.uint8, device="cuda")
+    b64.b64enc_device(d_in, d_in_off, d_out, d_out_off, scratch)
+    # decode it back
+    dec_off = np.arange(n + 1, dtype=np.int64) * ((unit + 2) // 3 * 3 + 1)
+    d_dec_off = torch.from_numpy(dec_off).cuda()
+    d_back = torch.zeros(int(dec_off[-1]), dtype=torch.uint8, device="cuda")
+    d_len = torch.zeros(n, dtype=torch.int64, device="cuda")
+    d_status = torch.zeros(n, dtype=torch.int64, device="cuda")
+    # encoded units are padded to 16-byte starts; hand the decoder exact unit extents
+    enc_len = b64.encoded_len(unit)
+    starts = torch.from_numpy(out_off[:-1]).cuda()
+    idx = (starts[:, None] + torch.arange(enc_len, device="cuda")[None, :]).reshape(-1)
+    d_enc = d_out[idx].contiguous()
+    enc_off = torch.arange(n + 1, dtype=torch.int64, device="cuda") * enc_len
+    scratch2 = torch.empty(b64.scratch_bytes(n, n * enc_len), dtype=torch.uint8, device="cuda")
+    b64.b64dec_device(d_enc, enc_off, d_back, d_dec_off, d_len, d_status, scratch2)
+    torch.cuda.synchronize()
+    assert bool((d_status == -1).all()) and bool((d_len == unit).all())
+    back = d_back.view(n, -1)[:, :unit].reshape(-1)
+    assert torch.equal(back, d_in)
+    lut = torch.zeros(256, dtype=torch.bool, device="cuda")
+    lut[torch.tensor(list(b"ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/="), device="cuda")] = True
+    assert bool(lut[d_enc.long()].all())
+    # spot-check a few units against the CPU checker
+    for i in (0, 1, n // 2, n - 1):
+        raw = d_in[i * unit:(i + 1) * unit].cpu().numpy().tobytes()
+        assert d_enc[i * enc_len:(i + 1) * enc_len].cpu().numpy().tobytes() == ob64.encode(raw)
+
+
+def test_empty_batch_and_empty_units(torch_cuda):
+    assert b64.b64enc(b"") == b""
+    assert b64.b64dec(b"") == b""
+    assert b64.b64enc_many([]) == []
+    assert b64.b64enc_many([b"", b"", b"a", b""]) == [b"", b"", b"YQ==", b""]
+    assert b64.b64dec_many([b"", b"YQ==", b""]) == [b"", b"a", b""]
+
+
+def test_secret_ceiling_unit(torch_cuda):
+    raw = workload.named_inputs(0)["f8"]          # just under the 1 MiB Secret limit
+    enc = b64.b64enc(raw)
+    assert len(enc) <= workload.SECRET_CEILING and enc == ob64.encode(raw)
+    assert b64.b64dec(enc) == raw
