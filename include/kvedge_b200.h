@@ -75,7 +75,7 @@ int kv_b64enc_plan_dev(const int64_t *d_in_off, int64_t n_units, int64_t total_i
                        const int64_t *d_out_off, void *d_scratch, size_t scratch_bytes,
                        void *stream);
 int kv_b64enc_run_dev(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
-                      int64_t total_in_bytes, char *d_out, const void *d_scratch,
+                      int64_t total_in_bytes, char *d_out, void *d_scratch,
                       size_t scratch_bytes, void *stream);
 
 /* Inverse of the above: what the Kubernetes API server / KubeVirt do to

@@ -117,7 +117,11 @@ plan_emit(const int64_t *__restrict__ in_off, const int64_t *__restrict__ out_of
         }
     }
     int first = base_sh + block_excl_scan(cnt, &total);
-    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) header[0] = base_sh + total;
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+        header[0] = base_sh + total;
+        header[1] = 0;  // tile counter and finished-block counter of the consuming kernel
+        header[2] = 0;
+    }
     for (int k = 0; k < cnt; ++k) {
         int64_t s = (int64_t)k * tile_in;
         TileDesc d;
@@ -133,42 +137,62 @@ plan_emit(const int64_t *__restrict__ in_off, const int64_t *__restrict__ out_of
 }
 
 // ----------------------------------------------------------------------------- encode
-// np = b0<<24 | b1<<16 | b2<<8 | (don't care).  Returns the four 6-bit values of the
-// 24-bit group, one per byte lane, first character in the lowest lane.
-__device__ __forceinline__ uint32_t sextets(uint32_t np) {
-    uint32_t x = np >> 26;
-    x |= (np >> 12) & 0x00003F00u;
-    x |= (np << 2) & 0x003F0000u;
-    x |= (np << 16) & 0x3F000000u;
-    return x;
-}
-
-// Four 6-bit values (one per byte lane) -> four RFC 4648 alphabet characters, branch
-// and table free.  Per lane:  c = v - 25 + 6[v>25] + 75[v<=51] + 15[v<=61] + 3[v>62].
-// The comparisons are carries into bit 7 of each lane (no lane ever overflows), and
-// the weighted flags are folded in with multiply-high, which runs on the FMA pipe and
-// leaves the ALU pipe for the adds and masks.  The lane sums end in [43, 122], so the
-// 32-bit arithmetic never lets one lane disturb the next.
-__device__ __forceinline__ uint32_t sextets_to_ascii(uint32_t x) {
-    uint32_t p1 = (x + 0x66666666u) & 0x80808080u;  // v > 25
-    uint32_t p2 = (0xB3B3B3B3u - x) & 0x80808080u;  // v <= 51
-    uint32_t p3 = (0xBDBDBDBDu - x) & 0x80808080u;  // v <= 61
-    uint32_t p4 = (x + 0x41414141u) & 0x80808080u;  // v > 62
-    uint32_t r = x - 0x19191919u;
-    r += __umulhi(p1, 6u << 25);
-    r += __umulhi(p2, 75u << 25);
-    r += __umulhi(p3, 15u << 25);
-    r += __umulhi(p4, 3u << 25);
+// One 3-byte group -> four RFC 4648 alphabet characters, branch and table free.
+//
+// np = b0<<24 | b1<<16 | b2<<8 | (don't care).  The four 6-bit values v0..v3 are moved
+// into byte lanes 0..3 (first character in the lowest lane) by three masks and four
+// multiplies (shifts done on the FMA pipe), already biased by -25 per lane:
+//     xb = x - 0x19191919,  x = v0 | v1<<8 | v2<<16 | v3<<24.
+// Per lane the character is  c = v - 25 + 6[v>25] + 75[v<=51] + 15[v<=61] + 3[v>62].
+// Each comparison is a carry into bit 7 of its lane (no lane ever overflows into the
+// next), and the weighted flags are folded in with multiply-high, again on the FMA
+// pipe, which leaves the ALU pipe -- the scarce resource of this kernel -- with the
+// byte permute, three masks and the four add+mask pairs.  Lane sums end in [43, 122],
+// so plain 32-bit arithmetic never lets one lane disturb its neighbour.
+// (Written in PTX so that the compiler front end cannot re-associate the sums back
+// into ALU-pipe shifts and adds.)
+__device__ __forceinline__ uint32_t encode_group(uint32_t np) {
+    uint32_t r;
+    asm("{\n\t"
+        ".reg .u32 m1, m2, m3, xb, t, p1, p2, p3, p4;\n\t"
+        "and.b32 m1, %1, 0x03F00000;\n\t"
+        "and.b32 m2, %1, 0x000FC000;\n\t"
+        "and.b32 m3, %1, 0x00003F00;\n\t"
+        "shr.u32 xb, %1, 26;\n\t"
+        "add.u32 xb, xb, 0xE6E6E6E7;\n\t"          // v0 - 0x19191919 (bias every lane by -25)
+        "mul.hi.u32 t, m1, 0x00100000;\n\t"        // v1 -> lane 1
+        "add.u32 xb, xb, t;\n\t"
+        "mad.lo.u32 xb, m2, 4, xb;\n\t"            // v2 -> lane 2
+        "mad.lo.u32 xb, m3, 65536, xb;\n\t"        // v3 -> lane 3
+        "add.u32 p1, xb, 0x7F7F7F7F;\n\t"          // bit 7 of each lane: v > 25
+        "sub.u32 p2, 0x9A9A9A9A, xb;\n\t"          //                     v <= 51
+        "sub.u32 p3, 0xA4A4A4A4, xb;\n\t"          //                     v <= 61
+        "add.u32 p4, xb, 0x5A5A5A5A;\n\t"          //                     v > 62
+        "and.b32 p1, p1, 0x80808080;\n\t"
+        "and.b32 p2, p2, 0x80808080;\n\t"
+        "and.b32 p3, p3, 0x80808080;\n\t"
+        "and.b32 p4, p4, 0x80808080;\n\t"
+        "mul.hi.u32 t, p1, 0x0C000000;\n\t"        // + 6 per flagged lane
+        "add.u32 xb, xb, t;\n\t"
+        "mul.hi.u32 t, p2, 0x96000000;\n\t"        // + 75
+        "add.u32 xb, xb, t;\n\t"
+        "mul.hi.u32 t, p3, 0x1E000000;\n\t"        // + 15
+        "add.u32 xb, xb, t;\n\t"
+        "mul.hi.u32 t, p4, 0x06000000;\n\t"        // + 3
+        "add.u32 %0, xb, t;\n\t"
+        "}"
+        : "=r"(r)
+        : "r"(np));
     return r;
 }
 
 // 12 input bytes in three little-endian words -> 16 output characters.
 __device__ __forceinline__ uint4 encode12(uint32_t a0, uint32_t a1, uint32_t a2) {
     uint4 r;
-    r.x = sextets_to_ascii(sextets(__byte_perm(a0, 0u, 0x0124)));
-    r.y = sextets_to_ascii(sextets(__byte_perm(a0, a1, 0x3455)));
-    r.z = sextets_to_ascii(sextets(__byte_perm(a1, a2, 0x2344)));
-    r.w = sextets_to_ascii(sextets(__byte_perm(a2, 0u, 0x1233)));
+    r.x = encode_group(__byte_perm(a0, 0u, 0x0124));
+    r.y = encode_group(__byte_perm(a0, a1, 0x3455));
+    r.z = encode_group(__byte_perm(a1, a2, 0x2344));
+    r.w = encode_group(__byte_perm(a2, 0u, 0x1233));
     return r;
 }
 
@@ -182,13 +206,84 @@ __device__ __forceinline__ void store_chars(char *dst, uint4 v, int nchars) {
     }
 }
 
-__global__ void __launch_bounds__(kThreads)
+// Edge thread: the unit's tail (fewer than 12 bytes, '=' padding) or a thread whose
+// word loads would leave the blob.  Byte loads, byte stores.
+__device__ __noinline__ void encode_edge(const uint8_t *p, char *q, int nvalid) {
+    uint32_t a[3] = {0u, 0u, 0u};
+#pragma unroll
+    for (int i = 0; i < 12; ++i)
+        if (i < nvalid) a[i >> 2] |= (uint32_t)p[i] << (8 * (i & 3));
+    uint4 v = encode12(a[0], a[1], a[2]);
+    const int rem = nvalid % 3, gi = nvalid / 3;
+    if (rem) {
+        uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+            if (g == gi)
+                w[g] = (rem == 1) ? ((w[g] & 0x0000FFFFu) | 0x3D3D0000u)
+                                  : ((w[g] & 0x00FFFFFFu) | 0x3D000000u);
+        v = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    store_chars(q, v, (nvalid + 2) / 3 * 4);
+}
+
+constexpr int kEncRows = kEncTileIn / (kThreads * 12);
+
+// All rows of one tile.  SHIFTED: the tile's first byte is not 4-byte aligned, so each
+// thread loads one more word and funnel-shifts.  STORE: 0 = 16-byte aligned destination
+// (one STG.128 per thread), 1 = 4-byte aligned (four STG.32), 2 = unaligned (bytes).
+// `fast_len` is `len` when word loads anywhere in the tile stay inside the blob, else 0.
+template <bool SHIFTED, int STORE>
+__device__ __forceinline__ void encode_tile_rows(const uint8_t *src, char *dst, int len,
+                                                 int fast_len, uint32_t sh) {
+    const uint32_t *wbase = reinterpret_cast<const uint32_t *>(src - sh) + threadIdx.x * 3;
+    const uint32_t s8 = sh * 8;
+#pragma unroll
+    for (int row = 0; row < kEncRows; ++row) {
+        const int off = row * (kThreads * 12) + (int)threadIdx.x * 12;
+        char *q = dst + (row * (kThreads * 16) + (int)threadIdx.x * 16);
+        if (off + 12 <= fast_len) {
+            const uint32_t *wp = wbase + row * (kThreads * 3);
+            uint32_t a0 = __ldg(wp), a1 = __ldg(wp + 1), a2 = __ldg(wp + 2);
+            if (SHIFTED) {
+                const uint32_t a3 = __ldg(wp + 3);
+                a0 = __funnelshift_r(a0, a1, s8);
+                a1 = __funnelshift_r(a1, a2, s8);
+                a2 = __funnelshift_r(a2, a3, s8);
+            }
+            const uint4 v = encode12(a0, a1, a2);
+            if (STORE == 0) {
+                *reinterpret_cast<uint4 *>(q) = v;
+            } else if (STORE == 1) {
+                uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
+                q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
+            } else {
+                store_chars(q, v, 16);
+            }
+        } else if (off < len) {
+            encode_edge(src + off, q, (len - off) < 12 ? (len - off) : 12);
+        } else {
+            break;
+        }
+    }
+}
+
+// Persistent grid; blocks pull tiles from a counter in the scratch header so that ragged
+// units (an 11 KiB config next to a 2.4 KB cloud-init text) cannot pile up on some SMs.
+// header: [0] n_tiles, [1] next tile, [2] blocks finished (the last one re-arms [1],[2]).
+__global__ void __launch_bounds__(kThreads, 8)
 b64enc_tiles(const uint8_t *__restrict__ in, char *__restrict__ out,
-             const TileDesc *__restrict__ desc, const int *__restrict__ header,
+             const TileDesc *__restrict__ desc, int *__restrict__ header,
              const int64_t *__restrict__ in_off, int64_t n_units) {
+    __shared__ int s_tile[2];
     const int n_tiles = header[0];
     const int64_t in_end = in_off[n_units];
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    if (threadIdx.x == 0) s_tile[0] = atomicAdd(&header[1], 1);
+    __syncthreads();
+    int tile = s_tile[0];
+    for (int it = 0; tile < n_tiles; ++it) {
+        int next = 0;
+        if (threadIdx.x == 0) next = atomicAdd(&header[1], 1);  // in flight during the tile
         const int4 *dp = reinterpret_cast<const int4 *>(desc + tile);
         const int4 d0 = __ldg(dp), d1 = __ldg(dp + 1);
         const int64_t in_pos = ((int64_t)(uint32_t)d0.y << 32) | (uint32_t)d0.x;
@@ -198,56 +293,29 @@ b64enc_tiles(const uint8_t *__restrict__ in, char *__restrict__ out,
         char *dst = out + out_pos;
         const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 3u);
         const uint32_t dalign = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
-#pragma unroll
-        for (int row = 0; row < kEncTileIn / (kThreads * 12); ++row) {
-            const int off = row * (kThreads * 12) + (int)threadIdx.x * 12;
-            if (off >= len) break;
-            const uint8_t *p = src + off;
-            char *q = dst + (row * (kThreads * 16) + (int)threadIdx.x * 16);
-            // Word loads may touch up to 3 bytes before and 4 after this thread's 12;
-            // keep them inside the blob.
-            const bool interior = (off + 12 <= len) && (in_pos + off + 16 <= in_end) &&
-                                  (in_pos + off >= 3);
-            if (interior) {
-                const uint32_t *wp = reinterpret_cast<const uint32_t *>(p - sh);
-                uint32_t a0 = __ldg(wp), a1 = __ldg(wp + 1), a2 = __ldg(wp + 2);
-                if (sh) {
-                    uint32_t a3 = __ldg(wp + 3);
-                    const uint32_t s8 = sh * 8;
-                    a0 = __funnelshift_r(a0, a1, s8);
-                    a1 = __funnelshift_r(a1, a2, s8);
-                    a2 = __funnelshift_r(a2, a3, s8);
-                }
-                const uint4 v = encode12(a0, a1, a2);
-                if (dalign == 0) {
-                    *reinterpret_cast<uint4 *>(q) = v;
-                } else if ((dalign & 3u) == 0) {
-                    uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
-                    q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
-                } else {
-                    store_chars(q, v, 16);
-                }
-            } else {
-                // Edge thread: the unit's tail (fewer than 12 bytes, '=' padding) or a
-                // thread whose word loads would leave the blob. Byte loads.
-                const int nvalid = (len - off) < 12 ? (len - off) : 12;
-                uint32_t a[3] = {0u, 0u, 0u};
-#pragma unroll
-                for (int i = 0; i < 12; ++i)
-                    if (i < nvalid) a[i >> 2] |= (uint32_t)p[i] << (8 * (i & 3));
-                uint4 v = encode12(a[0], a[1], a[2]);
-                const int rem = nvalid % 3, gi = nvalid / 3;
-                if (rem) {
-                    uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                    for (int g = 0; g < 4; ++g)
-                        if (g == gi)
-                            w[g] = (rem == 1) ? ((w[g] & 0x0000FFFFu) | 0x3D3D0000u)
-                                              : ((w[g] & 0x00FFFFFFu) | 0x3D000000u);
-                    v = make_uint4(w[0], w[1], w[2], w[3]);
-                }
-                store_chars(q, v, (nvalid + 2) / 3 * 4);
-            }
+        // Word loads touch up to 3 bytes before and 4 after a thread's 12 bytes: only take
+        // the word path when that stays inside the blob for the whole tile.
+        const int fast_len = (in_pos >= 3 && in_pos + len + 4 <= in_end) ? len : 0;
+        if (dalign == 0) {
+            if (sh == 0) encode_tile_rows<false, 0>(src, dst, len, fast_len, sh);
+            else encode_tile_rows<true, 0>(src, dst, len, fast_len, sh);
+        } else if ((dalign & 3u) == 0) {
+            if (sh == 0) encode_tile_rows<false, 1>(src, dst, len, fast_len, sh);
+            else encode_tile_rows<true, 1>(src, dst, len, fast_len, sh);
+        } else {
+            if (sh == 0) encode_tile_rows<false, 2>(src, dst, len, fast_len, sh);
+            else encode_tile_rows<true, 2>(src, dst, len, fast_len, sh);
+        }
+        if (threadIdx.x == 0) s_tile[(it + 1) & 1] = next;
+        __syncthreads();
+        tile = s_tile[(it + 1) & 1];
+    }
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(&header[2], 1) == (int)gridDim.x - 1) {
+            header[1] = 0;
+            header[2] = 0;
+            __threadfence();
         }
     }
 }
@@ -460,7 +528,7 @@ cudaError_t launch_b64enc_plan(const int64_t *d_in_off, int64_t n_units, int64_t
 }
 
 cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
-                              int64_t total_in_bytes, char *d_out, const void *d_scratch,
+                              int64_t total_in_bytes, char *d_out, void *d_scratch,
                               size_t scratch_bytes, cudaStream_t stream, int sm_count) {
     if (n_units <= 0) return cudaSuccess;
     ScratchLayout L = scratch_layout(n_units, total_in_bytes, kEncTileIn);
@@ -475,10 +543,10 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
     int64_t grid = (int64_t)sm_count * g_occ_enc;
     if (grid > L.max_tiles) grid = L.max_tiles;
     if (grid < 1) grid = 1;
-    const char *base = static_cast<const char *>(d_scratch);
+    char *base = static_cast<char *>(d_scratch);
     b64enc_tiles<<<(unsigned)grid, kThreads, 0, stream>>>(
         d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
-        reinterpret_cast<const int *>(base), d_in_off, n_units);
+        reinterpret_cast<int *>(base), d_in_off, n_units);
     return cudaGetLastError();
 }
 

@@ -48,7 +48,7 @@ cudaError_t launch_b64enc_plan(const int64_t *d_in_off, int64_t n_units, int64_t
                                const int64_t *d_out_off, void *d_scratch, size_t scratch_bytes,
                                cudaStream_t stream);
 cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
-                              int64_t total_in_bytes, char *d_out, const void *d_scratch,
+                              int64_t total_in_bytes, char *d_out, void *d_scratch,
                               size_t scratch_bytes, cudaStream_t stream, int sm_count);
 
 cudaError_t launch_b64dec(const char *d_in, const int64_t *d_in_off, int64_t n_units,

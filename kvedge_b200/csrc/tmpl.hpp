@@ -1,0 +1,102 @@
+// Go text/template + Sprig subset: the host side of the render path.
+//
+// What Helm does with deployment/helm/templates/* of the reference, restricted to the
+// constructs that chart (and neighbours a chart author would reach for next) uses:
+//   actions, {{- -}} trimming, comments ......... templates/_helper.tpl:1-75
+//   define / include / template ................. _helper.tpl:6,13,20,31
+//   if / else / with / range / variables ........ _helper.tpl:22-24, aziot-edge-vm-service.yaml:1,18
+//   default trunc trimSuffix printf replace quote indent b64enc eq ...
+//                                                 _helper.tpl:7,14,23; aziot-edge-vm.yaml:13;
+//                                                 aziot-edge-*-secret.yaml:6
+// Strings are byte strings end to end (Go semantics): `trunc` slices bytes and
+// --set-file content passes through untouched.
+#pragma once
+#include <cstdint>
+#include <functional>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace kvedge {
+namespace tmpl {
+
+struct Error : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+struct Value;
+using List = std::vector<Value>;
+using Map = std::map<std::string, Value>;
+
+struct Value {
+    enum Kind { Nil, NoValue, Bool, Int, Float, String, ListK, MapK, StructK };
+    Kind kind = Nil;
+    bool b = false;
+    int64_t i = 0;
+    double f = 0;
+    std::string s;                 // String payload; for StructK the Go type name
+    std::shared_ptr<List> list;
+    std::shared_ptr<Map> map;      // MapK and StructK
+
+    static Value nil() { return Value(); }
+    static Value novalue() { Value v; v.kind = NoValue; return v; }
+    static Value boolean(bool x) { Value v; v.kind = Bool; v.b = x; return v; }
+    static Value integer(int64_t x) { Value v; v.kind = Int; v.i = x; return v; }
+    static Value number(double x) { Value v; v.kind = Float; v.f = x; return v; }
+    static Value str(std::string x) { Value v; v.kind = String; v.s = std::move(x); return v; }
+    static Value make_list() { Value v; v.kind = ListK; v.list = std::make_shared<List>(); return v; }
+    static Value make_map() { Value v; v.kind = MapK; v.map = std::make_shared<Map>(); return v; }
+    static Value make_struct(std::string type_name) {
+        Value v; v.kind = StructK; v.s = std::move(type_name); v.map = std::make_shared<Map>(); return v;
+    }
+    bool is_nilish() const { return kind == Nil || kind == NoValue; }
+};
+
+bool truth(const Value &v);            // text/template truth
+std::string go_print(const Value &v);  // fmt.Fprint of one value
+std::string format_float(double f);    // Go %v of a float64
+std::string go_quote(const std::string &s);  // strconv.Quote
+Value deep_copy(const Value &v);
+
+// A b64enc site whose evaluation is deferred to the GPU: the input bytes are kept and the
+// output carries a placeholder of exactly the encoded length.
+struct Pending {
+    std::string input;
+    size_t encoded_len = 0;
+};
+
+// Called for every `b64enc` the executor cannot defer (its result feeds another function).
+using ImmediateEncoder = std::function<std::string(const std::string &)>;
+
+struct Node;
+using NodeList = std::vector<std::shared_ptr<Node>>;
+
+class TemplateSet {
+  public:
+    TemplateSet();
+    // Parse one file; `define` blocks inside it land in the shared namespace.
+    void parse(const std::string &name, const std::string &src);
+    bool has(const std::string &name) const { return templates_.count(name) != 0; }
+
+    struct ExecOptions {
+        bool defer_b64 = false;             // leave top-level `... | b64enc` sites pending
+        std::vector<Pending> *pending = nullptr;
+        ImmediateEncoder encode;            // required whenever a b64enc must run now
+        ImmediateEncoder decode;            // b64dec (optional)
+    };
+    std::string execute(const std::string &name, const Value &data, const ExecOptions &opt) const;
+
+    // Placeholder protocol (see render.cpp): 4 id bytes in [0x10,0x20) then 0x01 filler.
+    static std::string placeholder(size_t id, size_t encoded_len);
+    static bool has_sentinel_bytes(const std::string &s);
+    static constexpr size_t kMaxPending = 65536;
+
+  private:
+    friend struct Exec;
+    std::map<std::string, NodeList> templates_;
+};
+
+}  // namespace tmpl
+}  // namespace kvedge
