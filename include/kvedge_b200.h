@@ -106,6 +106,62 @@ int kv_b64dec(const char *in, size_t n, uint8_t *out, size_t *out_n, size_t *err
 int kv_b64dec_batch(const char *in, const int64_t *in_off, int64_t n_units, uint8_t *out,
                     const int64_t *out_off, int64_t *out_len, int64_t *status);
 
+/* ---- render path: values -> templates -> (pending b64enc) -> `helm template` stream -----
+ * What Helm does with the reference's chart (README.md:60:
+ *   helm install --generate-name . --set publicSshKey=...,nameOverride=... --set-file azIotEdgeConfig=config.toml)
+ * restricted to the Go-template / Sprig subset the chart uses
+ * (deployment/helm/templates/_helper.tpl:1-75 and the six resource templates),
+ * with deployment/helm/.helmignore honoured (l.25 disables the HTTP-disk DataVolume).
+ * A release is first *planned*: every template is rendered on the host, but each top-level
+ * `... | b64enc` site (aziot-edge-runtime-config-secret.yaml:6, aziot-edge-vm-cloud-init-secret.yaml:6)
+ * is left pending; kv_release_encode_gpu then encodes all pending payloads in one GPU batch.
+ * A b64enc whose result feeds another function is evaluated at once (still on the GPU).   */
+typedef struct kv_chart kv_chart;
+typedef struct kv_release kv_release;
+
+/* Value overrides in Helm's own flag syntax (pkg/strvals). `blob_*` is --set-file with the
+ * file content already in memory (verbatim bytes). */
+typedef struct kv_overrides {
+    const char *const *set;        int n_set;         /* --set k=v[,k=v]          */
+    const char *const *set_string; int n_set_string;  /* --set-string k=v         */
+    const char *const *set_file;   int n_set_file;    /* --set-file k=path        */
+    const char *const *blob_keys;  const uint8_t *const *blob_data;
+    const size_t *blob_len;        int n_blob;        /* --set-file, from memory  */
+} kv_overrides;
+
+int kv_chart_load(const char *chart_dir, kv_chart **out);
+void kv_chart_free(kv_chart *chart);
+/* Render one release with its b64enc sites pending (no GPU work yet). */
+int kv_release_plan(const kv_chart *chart, const char *release_name, const char *ns,
+                    const kv_overrides *overrides, kv_release **out);
+int kv_release_pending_count(const kv_release *r);
+/* Input bytes of pending site i (valid until the release is freed). */
+int kv_release_pending_input(const kv_release *r, int i, const uint8_t **data, size_t *len);
+/* Supply the encoding of pending site i from outside (a caller that batches many releases
+ * through kv_b64enc_batch_dev itself); len must be kv_b64enc_len(input len). */
+int kv_release_pending_fill(kv_release *r, int i, const char *enc, size_t len);
+/* Encode every pending site on the GPU (one kv_b64enc_batch call). */
+int kv_release_encode_gpu(kv_release *r);
+/* `helm template` stream ("---\n# Source: <chart>/templates/<file>\n<doc>\n" per document, in
+ * Helm's install order) and the NOTES text (what `helm install` prints; the reference's
+ * only recorded real-Helm output is deployment/az-iot-edge-k8s-kubevirt-ascii.cast:2294).
+ * Fail with KV_EINVAL while sites are still pending. Pointers stay valid until free. */
+int kv_release_manifest(kv_release *r, const char **data, size_t *len);
+int kv_release_notes(kv_release *r, const char **data, size_t *len);
+void kv_release_free(kv_release *r);
+/* One call: load, plan, encode on the GPU, frame. *out is malloc'd: release with kv_free. */
+int kv_helm_template(const char *chart_dir, const char *release_name, const char *ns,
+                     const kv_overrides *overrides, char **out, size_t *out_len);
+/* n_releases installs of one chart (the reference's only multiplicity: re-installing with
+ * another nameOverride, README.md:72) rendered together: all Secret payloads of the fleet
+ * go through ONE GPU batch. out_off receives n_releases+1 offsets into *out (kv_free). */
+int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *release_names,
+                      const char *ns, const kv_overrides *overrides, char **out, int64_t *out_off);
+/* `helm lint` equivalent (BASELINE.json config 1). *messages: newline-separated, kv_free. */
+int kv_helm_lint(const char *chart_dir, const kv_overrides *overrides, int *ok, char **messages,
+                 size_t *len);
+void kv_free(void *p);
+
 /* Select the CUDA device the host-buffer entry points use (default 0). */
 int kv_set_device(int device);
 /* Release the per-device staging buffers and streams held by the host-buffer path. */

@@ -36,9 +36,35 @@ SIGNATURES = {
                             C.POINTER(C.c_size_t)]),
     "kv_b64dec_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                   C.c_void_p, C.c_void_p]),
+    "kv_chart_load": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "kv_chart_free": (None, [C.c_void_p]),
+    "kv_release_plan": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.c_void_p, C.POINTER(C.c_void_p)]),
+    "kv_release_pending_count": (C.c_int, [C.c_void_p]),
+    "kv_release_pending_input": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
+    "kv_release_pending_fill": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_size_t]),
+    "kv_release_encode_gpu": (C.c_int, [C.c_void_p]),
+    "kv_release_manifest": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
+    "kv_release_notes": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
+    "kv_release_free": (None, [C.c_void_p]),
+    "kv_helm_template": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_void_p, C.POINTER(C.c_void_p),
+                                   C.POINTER(C.c_size_t)]),
+    "kv_fleet_template": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_char_p, C.c_void_p,
+                                    C.POINTER(C.c_void_p), C.c_void_p]),
+    "kv_helm_lint": (C.c_int, [C.c_char_p, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_void_p),
+                               C.POINTER(C.c_size_t)]),
+    "kv_free": (None, [C.c_void_p]),
     "kv_set_device": (C.c_int, [C.c_int]),
     "kv_shutdown": (None, []),
 }
+
+
+class KvOverrides(C.Structure):
+    """struct kv_overrides of include/kvedge_b200.h."""
+    _fields_ = [("set", C.POINTER(C.c_char_p)), ("n_set", C.c_int),
+                ("set_string", C.POINTER(C.c_char_p)), ("n_set_string", C.c_int),
+                ("set_file", C.POINTER(C.c_char_p)), ("n_set_file", C.c_int),
+                ("blob_keys", C.POINTER(C.c_char_p)), ("blob_data", C.POINTER(C.c_void_p)),
+                ("blob_len", C.POINTER(C.c_size_t)), ("n_blob", C.c_int)]
 
 
 class KvError(RuntimeError):

@@ -236,6 +236,12 @@ int run_host_batch(int mode, const char *in, const int64_t *in_off, int64_t n_un
 
 extern "C" {
 
+// shared with render_capi.cpp (not part of the public header)
+int kv_set_last_error_(int code, const char *msg) {
+    g_err = msg ? msg : "";
+    return code;
+}
+
 int kv_version(void) { return 100; }
 
 const char *kv_last_error(void) { return g_err.c_str(); }

@@ -1,0 +1,752 @@
+// Chart loading, values handling and manifest framing (see chart.hpp).
+#include "chart.hpp"
+
+#include <dirent.h>
+#include <fnmatch.h>
+#include <sys/stat.h>
+
+#include <algorithm>
+#include <cerrno>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+
+namespace kvedge {
+namespace chart {
+
+using tmpl::Error;
+
+// ============================================================================ helpers
+static bool is_ws(char c) { return c == ' ' || c == '\t' || c == '\r' || c == '\n' || c == '\v' || c == '\f'; }
+
+std::string trim_space(const std::string &s) {
+    size_t a = 0, b = s.size();
+    while (a < b && is_ws(s[a])) ++a;
+    while (b > a && is_ws(s[b - 1])) --b;
+    return s.substr(a, b - a);
+}
+
+static std::string read_file(const std::string &path) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f) throw Error("open " + path + ": " + strerror(errno));
+    std::ostringstream ss;
+    ss << f.rdbuf();
+    return ss.str();
+}
+
+static bool file_exists(const std::string &p) {
+    struct stat st;
+    return stat(p.c_str(), &st) == 0;
+}
+
+// ============================================================================ YAML subset
+namespace {
+
+bool in_set(const std::string &s, std::initializer_list<const char *> set) {
+    for (const char *x : set)
+        if (s == x) return true;
+    return false;
+}
+
+Value resolve_plain(const std::string &s, bool json_numbers) {
+    if (in_set(s, {"", "~", "null", "Null", "NULL"})) return Value::nil();
+    if (in_set(s, {"y", "Y", "yes", "Yes", "YES", "on", "On", "ON", "true", "True", "TRUE"})) return Value::boolean(true);
+    if (in_set(s, {"n", "N", "no", "No", "NO", "off", "Off", "OFF", "false", "False", "FALSE"})) return Value::boolean(false);
+    std::string plain;
+    for (char c : s)
+        if (c != '_') plain.push_back(c);
+    // integers: [-+]? (0x.. | 0o.. | 0b.. | 0[0-7]* | [1-9][0-9]*)
+    {
+        size_t i = 0;
+        bool neg = false;
+        if (i < plain.size() && (plain[i] == '-' || plain[i] == '+')) { neg = plain[i] == '-'; ++i; }
+        std::string body = plain.substr(i);
+        int base = 0;
+        std::string digits;
+        if (body.size() > 2 && body[0] == '0' && (body[1] == 'x' || body[1] == 'X')) { base = 16; digits = body.substr(2); }
+        else if (body.size() > 2 && body[0] == '0' && (body[1] == 'o' || body[1] == 'O')) { base = 8; digits = body.substr(2); }
+        else if (body.size() > 2 && body[0] == '0' && (body[1] == 'b' || body[1] == 'B')) { base = 2; digits = body.substr(2); }
+        else if (!body.empty() && body[0] == '0') { base = 8; digits = body.size() > 1 ? body.substr(1) : "0"; }
+        else if (!body.empty() && body[0] >= '1' && body[0] <= '9') { base = 10; digits = body; }
+        bool ok = base != 0 && !digits.empty();
+        for (char c : digits) {
+            int d = (c >= '0' && c <= '9') ? c - '0' : (c >= 'a' && c <= 'f') ? c - 'a' + 10 : (c >= 'A' && c <= 'F') ? c - 'A' + 10 : 99;
+            if (d >= base) ok = false;
+        }
+        if (ok) {
+            errno = 0;
+            unsigned long long mag = strtoull(digits.c_str(), nullptr, base);
+            if (errno == 0) {
+                if (json_numbers) return Value::number(neg ? -(double)mag : (double)mag);
+                if (mag <= (unsigned long long)INT64_MAX) return Value::integer(neg ? -(int64_t)mag : (int64_t)mag);
+                return Value::number(neg ? -(double)mag : (double)mag);
+            }
+        }
+    }
+    // floats: [-+]?(\.[0-9]+|[0-9]+(\.[0-9]*)?)([eE][-+]?[0-9]+)?
+    {
+        size_t i = 0, n = plain.size();
+        if (i < n && (plain[i] == '-' || plain[i] == '+')) ++i;
+        size_t d0 = i;
+        while (i < n && isdigit((unsigned char)plain[i])) ++i;
+        bool int_digits = i > d0, frac_digits = false;
+        if (i < n && plain[i] == '.') {
+            ++i;
+            size_t f0 = i;
+            while (i < n && isdigit((unsigned char)plain[i])) ++i;
+            frac_digits = i > f0;
+        }
+        bool ok = int_digits || frac_digits;
+        if (ok && i < n && (plain[i] == 'e' || plain[i] == 'E')) {
+            ++i;
+            if (i < n && (plain[i] == '-' || plain[i] == '+')) ++i;
+            size_t e0 = i;
+            while (i < n && isdigit((unsigned char)plain[i])) ++i;
+            if (i == e0) ok = false;
+        }
+        if (ok && i == n && n > 0) return Value::number(strtod(plain.c_str(), nullptr));
+    }
+    if (in_set(plain, {".inf", ".Inf", ".INF", "+.inf", "+.Inf", "+.INF"})) return Value::number(INFINITY);
+    if (in_set(plain, {"-.inf", "-.Inf", "-.INF"})) return Value::number(-INFINITY);
+    if (in_set(plain, {".nan", ".NaN", ".NAN"})) return Value::number(NAN);
+    return Value::str(s);
+}
+
+void append_utf8(std::string &o, uint32_t cp) {
+    if (cp < 0x80) o.push_back((char)cp);
+    else if (cp < 0x800) { o.push_back((char)(0xC0 | (cp >> 6))); o.push_back((char)(0x80 | (cp & 0x3F))); }
+    else if (cp < 0x10000) {
+        o.push_back((char)(0xE0 | (cp >> 12))); o.push_back((char)(0x80 | ((cp >> 6) & 0x3F))); o.push_back((char)(0x80 | (cp & 0x3F)));
+    } else {
+        o.push_back((char)(0xF0 | (cp >> 18))); o.push_back((char)(0x80 | ((cp >> 12) & 0x3F)));
+        o.push_back((char)(0x80 | ((cp >> 6) & 0x3F))); o.push_back((char)(0x80 | (cp & 0x3F)));
+    }
+}
+
+struct Yaml {
+    std::vector<std::string> lines;
+    size_t cur = 0;
+    bool json_numbers;
+
+    static int indent_of(const std::string &l) {
+        int n = 0;
+        while ((size_t)n < l.size() && l[(size_t)n] == ' ') ++n;
+        return n;
+    }
+    static bool blank(const std::string &l) {
+        for (char c : l) {
+            if (c == '#') return true;
+            if (!is_ws(c)) return false;
+        }
+        return true;
+    }
+    void skip_blank() {
+        while (cur < lines.size() && (blank(lines[cur]) || lines[cur].compare(0, 3, "---") == 0 && cur == 0)) ++cur;
+    }
+    // strip a trailing comment (a '#' preceded by white space, outside quotes)
+    static std::string strip_comment(const std::string &s) {
+        bool sq = false, dq = false;
+        for (size_t i = 0; i < s.size(); ++i) {
+            char c = s[i];
+            if (dq) { if (c == '\\') ++i; else if (c == '"') dq = false; continue; }
+            if (sq) { if (c == '\'') sq = false; continue; }
+            if (c == '"' && (i == 0 || is_ws(s[i - 1]) || s[i - 1] == ':' || s[i - 1] == '[' || s[i - 1] == ',' || s[i - 1] == '{')) { dq = true; continue; }
+            if (c == '\'' && (i == 0 || is_ws(s[i - 1]) || s[i - 1] == '[' || s[i - 1] == ',' || s[i - 1] == '{')) { sq = true; continue; }
+            if (c == '#' && (i == 0 || is_ws(s[i - 1]))) return s.substr(0, i);
+        }
+        return s;
+    }
+    // position of the ':' that ends a mapping key in `s` (content without indent), or npos
+    static size_t key_colon(const std::string &s) {
+        if (s.empty()) return std::string::npos;
+        size_t i = 0;
+        if (s[0] == '"' || s[0] == '\'') {
+            char q = s[0];
+            ++i;
+            while (i < s.size() && s[i] != q) {
+                if (q == '"' && s[i] == '\\') ++i;
+                ++i;
+            }
+            ++i;
+            while (i < s.size() && s[i] == ' ') ++i;
+            if (i < s.size() && s[i] == ':' && (i + 1 == s.size() || is_ws(s[i + 1]))) return i;
+            return std::string::npos;
+        }
+        if (s[0] == '[' || s[0] == '{' || s[0] == '|' || s[0] == '>') return std::string::npos;
+        for (; i < s.size(); ++i) {
+            if (s[i] == ':' && (i + 1 == s.size() || is_ws(s[i + 1]))) return i;
+            if (s[i] == '#' && i > 0 && is_ws(s[i - 1])) return std::string::npos;
+        }
+        return std::string::npos;
+    }
+    std::string unquote_double(const std::string &s, size_t *end) {
+        std::string o;
+        size_t i = 1;
+        for (; i < s.size() && s[i] != '"'; ++i) {
+            char c = s[i];
+            if (c != '\\') { o.push_back(c); continue; }
+            ++i;
+            if (i >= s.size()) break;
+            switch (s[i]) {
+            case 'n': o.push_back('\n'); break;
+            case 't': o.push_back('\t'); break;
+            case 'r': o.push_back('\r'); break;
+            case '0': o.push_back('\0'); break;
+            case 'a': o.push_back(7); break;
+            case 'b': o.push_back(8); break;
+            case 'f': o.push_back(12); break;
+            case 'v': o.push_back(11); break;
+            case 'e': o.push_back(27); break;
+            case ' ': o.push_back(' '); break;
+            case '"': o.push_back('"'); break;
+            case '/': o.push_back('/'); break;
+            case '\\': o.push_back('\\'); break;
+            case 'N': append_utf8(o, 0x85); break;
+            case '_': append_utf8(o, 0xA0); break;
+            case 'x': o.push_back((char)strtol(s.substr(i + 1, 2).c_str(), nullptr, 16)); i += 2; break;
+            case 'u': append_utf8(o, (uint32_t)strtol(s.substr(i + 1, 4).c_str(), nullptr, 16)); i += 4; break;
+            case 'U': append_utf8(o, (uint32_t)strtol(s.substr(i + 1, 8).c_str(), nullptr, 16)); i += 8; break;
+            default: throw Error(std::string("yaml: unknown escape \\") + s[i]);
+            }
+        }
+        if (i >= s.size()) throw Error("yaml: unterminated double-quoted scalar");
+        *end = i + 1;
+        return o;
+    }
+    std::string unquote_single(const std::string &s, size_t *end) {
+        std::string o;
+        size_t i = 1;
+        for (; i < s.size(); ++i) {
+            if (s[i] == '\'') {
+                if (i + 1 < s.size() && s[i + 1] == '\'') { o.push_back('\''); ++i; continue; }
+                break;
+            }
+            o.push_back(s[i]);
+        }
+        if (i >= s.size()) throw Error("yaml: unterminated single-quoted scalar");
+        *end = i + 1;
+        return o;
+    }
+    // flow collection or scalar from one piece of text
+    Value parse_flow(const std::string &s, size_t &i) {
+        while (i < s.size() && is_ws(s[i])) ++i;
+        if (i >= s.size()) return Value::nil();
+        if (s[i] == '[') {
+            Value v = Value::make_list();
+            ++i;
+            for (;;) {
+                while (i < s.size() && is_ws(s[i])) ++i;
+                if (i >= s.size()) throw Error("yaml: unterminated flow sequence");
+                if (s[i] == ']') { ++i; break; }
+                v.list->push_back(parse_flow(s, i));
+                while (i < s.size() && is_ws(s[i])) ++i;
+                if (i < s.size() && s[i] == ',') ++i;
+            }
+            return v;
+        }
+        if (s[i] == '{') {
+            Value v = Value::make_map();
+            ++i;
+            for (;;) {
+                while (i < s.size() && is_ws(s[i])) ++i;
+                if (i >= s.size()) throw Error("yaml: unterminated flow mapping");
+                if (s[i] == '}') { ++i; break; }
+                Value k = parse_flow_scalar(s, i, true);
+                while (i < s.size() && is_ws(s[i])) ++i;
+                Value val;
+                if (i < s.size() && s[i] == ':') { ++i; val = parse_flow(s, i); }
+                (*v.map)[tmpl::go_print(k)] = val;
+                while (i < s.size() && is_ws(s[i])) ++i;
+                if (i < s.size() && s[i] == ',') ++i;
+            }
+            return v;
+        }
+        return parse_flow_scalar(s, i, false);
+    }
+    Value parse_flow_scalar(const std::string &s, size_t &i, bool is_key) {
+        while (i < s.size() && is_ws(s[i])) ++i;
+        if (i < s.size() && s[i] == '"') {
+            size_t e;
+            std::string sub = s.substr(i);
+            std::string o = unquote_double(sub, &e);
+            i += e;
+            return Value::str(o);
+        }
+        if (i < s.size() && s[i] == '\'') {
+            size_t e;
+            std::string sub = s.substr(i);
+            std::string o = unquote_single(sub, &e);
+            i += e;
+            return Value::str(o);
+        }
+        size_t j = i;
+        while (j < s.size() && s[j] != ',' && s[j] != ']' && s[j] != '}' &&
+               !(is_key && s[j] == ':' ) && !(s[j] == ':' && j + 1 < s.size() && is_ws(s[j + 1])))
+            ++j;
+        std::string tok = trim_space(s.substr(i, j - i));
+        i = j;
+        return resolve_plain(tok, json_numbers);
+    }
+    Value scalar_from_text(const std::string &text) {
+        std::string t = trim_space(text);
+        if (t.empty()) return Value::nil();
+        if (t[0] == '"') { size_t e; std::string o = unquote_double(t, &e); return Value::str(o); }
+        if (t[0] == '\'') { size_t e; std::string o = unquote_single(t, &e); return Value::str(o); }
+        if (t[0] == '[' || t[0] == '{') { size_t i = 0; return parse_flow(t, i); }
+        return resolve_plain(t, json_numbers);
+    }
+    Value block_scalar(const std::string &header, int parent_indent) {
+        bool literal = header[0] == '|';
+        char chomp = 'c';
+        int explicit_indent = 0;
+        for (size_t i = 1; i < header.size(); ++i) {
+            if (header[i] == '-') chomp = 's';
+            else if (header[i] == '+') chomp = 'k';
+            else if (isdigit((unsigned char)header[i])) explicit_indent = header[i] - '0';
+        }
+        std::vector<std::string> body;
+        int bi = explicit_indent ? parent_indent + explicit_indent : -1;
+        while (cur < lines.size()) {
+            const std::string &l = lines[cur];
+            bool empty = trim_space(l).empty();
+            int ind = indent_of(l);
+            if (!empty) {
+                if (bi < 0) {
+                    if (ind <= parent_indent) break;
+                    bi = ind;
+                }
+                if (ind < bi) break;
+            }
+            body.push_back(empty ? "" : l.substr((size_t)std::min<int>(bi < 0 ? ind : bi, (int)l.size())));
+            ++cur;
+        }
+        size_t trailing = 0;
+        while (!body.empty() && body.back().empty()) { body.pop_back(); ++trailing; }
+        std::string o;
+        if (literal) {
+            for (size_t i = 0; i < body.size(); ++i) { o += body[i]; if (i + 1 < body.size()) o += "\n"; }
+        } else {
+            for (size_t i = 0; i < body.size(); ++i) {
+                o += body[i];
+                if (i + 1 < body.size()) {
+                    if (body[i + 1].empty()) { o += "\n"; while (i + 1 < body.size() && body[i + 1].empty()) { ++i; if (i + 1 < body.size() && body[i + 1].empty()) o += "\n"; } }
+                    else if (body[i].empty() || body[i][0] == ' ' || body[i + 1][0] == ' ') o += "\n";
+                    else o += " ";
+                }
+            }
+        }
+        if (!body.empty()) {
+            if (chomp == 'c') o += "\n";
+            else if (chomp == 'k') o += std::string(trailing + 1, '\n');
+        }
+        return Value::str(o);
+    }
+    Value parse_value_after_key(const std::string &rest_raw, int ind) {
+        std::string rest = trim_space(strip_comment(rest_raw));
+        if (!rest.empty() && (rest[0] == '|' || rest[0] == '>')) return block_scalar(rest, ind);
+        if (!rest.empty()) return scalar_from_text(rest);
+        // value on the following lines
+        size_t save = cur;
+        skip_blank();
+        if (cur < lines.size()) {
+            int ni = indent_of(lines[cur]);
+            std::string c = lines[cur].substr((size_t)ni);
+            if (ni > ind) return parse_block(ni);
+            if (ni == ind && (c.compare(0, 2, "- ") == 0 || c == "-")) return parse_seq(ni);
+        }
+        cur = save;
+        return Value::nil();
+    }
+    Value parse_map(int ind) {
+        Value v = Value::make_map();
+        for (;;) {
+            skip_blank();
+            if (cur >= lines.size()) break;
+            if (indent_of(lines[cur]) != ind) {
+                if (indent_of(lines[cur]) > ind) throw Error("yaml: bad indentation at line " + std::to_string(cur + 1));
+                break;
+            }
+            std::string c = lines[cur].substr((size_t)ind);
+            size_t kc = key_colon(c);
+            if (kc == std::string::npos) break;
+            std::string key_txt = trim_space(c.substr(0, kc));
+            std::string key;
+            if (!key_txt.empty() && key_txt[0] == '"') { size_t e; key = unquote_double(key_txt, &e); }
+            else if (!key_txt.empty() && key_txt[0] == '\'') { size_t e; key = unquote_single(key_txt, &e); }
+            else key = key_txt;
+            ++cur;
+            (*v.map)[key] = parse_value_after_key(c.substr(kc + 1), ind);
+        }
+        return v;
+    }
+    Value parse_seq(int ind) {
+        Value v = Value::make_list();
+        for (;;) {
+            skip_blank();
+            if (cur >= lines.size() || indent_of(lines[cur]) != ind) break;
+            std::string c = lines[cur].substr((size_t)ind);
+            if (!(c.compare(0, 2, "- ") == 0 || c == "-")) break;
+            std::string item = c.size() > 1 ? c.substr(2) : "";
+            size_t lead = 0;
+            while (lead < item.size() && item[lead] == ' ') ++lead;
+            std::string body = item.substr(lead);
+            if (trim_space(strip_comment(body)).empty()) {
+                ++cur;
+                size_t save = cur;
+                skip_blank();
+                if (cur < lines.size() && indent_of(lines[cur]) > ind) v.list->push_back(parse_block(indent_of(lines[cur])));
+                else { cur = save; v.list->push_back(Value::nil()); }
+                continue;
+            }
+            if (key_colon(body) != std::string::npos) {
+                // "- key: value": a mapping that starts on the dash line
+                int vi = ind + 2 + (int)lead;
+                lines[cur] = std::string((size_t)vi, ' ') + body;
+                v.list->push_back(parse_map(vi));
+                continue;
+            }
+            ++cur;
+            std::string t = trim_space(strip_comment(body));
+            if (t[0] == '|' || t[0] == '>') v.list->push_back(block_scalar(t, ind));
+            else v.list->push_back(scalar_from_text(t));
+        }
+        return v;
+    }
+    Value parse_block(int ind) {
+        skip_blank();
+        if (cur >= lines.size()) return Value::nil();
+        std::string c = lines[cur].substr((size_t)indent_of(lines[cur]));
+        if (c.compare(0, 2, "- ") == 0 || c == "-") return parse_seq(indent_of(lines[cur]));
+        if (key_colon(c) != std::string::npos) return parse_map(indent_of(lines[cur]));
+        ++cur;
+        (void)ind;
+        return scalar_from_text(strip_comment(c));
+    }
+};
+
+}  // namespace
+
+Value parse_yaml(const std::string &text, bool json_numbers) {
+    Yaml y;
+    y.json_numbers = json_numbers;
+    size_t i = 0;
+    while (i <= text.size()) {
+        size_t j = text.find('\n', i);
+        if (j == std::string::npos) j = text.size();
+        std::string l = text.substr(i, j - i);
+        if (!l.empty() && l.back() == '\r') l.pop_back();
+        for (char c : l) {
+            if (c == '\t' ) { /* tabs are not indentation in YAML; keep as content */ break; }
+            if (c != ' ') break;
+        }
+        y.lines.push_back(l);
+        i = j + 1;
+    }
+    y.skip_blank();
+    if (y.cur >= y.lines.size()) return Value::nil();
+    Value v = y.parse_block(0);
+    y.skip_blank();
+    if (y.cur < y.lines.size() && y.lines[y.cur].compare(0, 3, "...") != 0 && y.lines[y.cur].compare(0, 3, "---") != 0)
+        throw Error("yaml: could not parse line " + std::to_string(y.cur + 1) + ": " + y.lines[y.cur]);
+    return v;
+}
+
+// ============================================================================ strvals
+namespace {
+
+Value set_typed(const std::string &val, bool force_string) {
+    if (force_string) return Value::str(val);
+    std::string low = val;
+    for (auto &c : low) c = (char)tolower((unsigned char)c);
+    if (low == "true") return Value::boolean(true);
+    if (low == "false") return Value::boolean(false);
+    if (low == "null") return Value::nil();
+    if (val == "0") return Value::integer(0);
+    if (!val.empty() && val[0] != '0') {
+        size_t i = (val[0] == '-' || val[0] == '+') ? 1 : 0;
+        bool digits = i < val.size();
+        for (size_t k = i; k < val.size(); ++k)
+            if (!isdigit((unsigned char)val[k])) digits = false;
+        if (digits) {
+            errno = 0;
+            long long v = strtoll(val.c_str(), nullptr, 10);
+            if (errno == 0) return Value::integer(v);
+        }
+    }
+    return Value::str(val);
+}
+
+std::vector<std::pair<std::string, std::string>> split_set(const std::string &s) {
+    std::vector<std::pair<std::string, std::string>> pairs;
+    size_t i = 0, n = s.size();
+    while (i < n) {
+        std::string key;
+        while (i < n && s[i] != '=') {
+            if (s[i] == '\\' && i + 1 < n) { key += s.substr(i, 2); i += 2; continue; }
+            if (s[i] == ',') throw Error("key \"" + key + "\" has no value");
+            key.push_back(s[i++]);
+        }
+        if (i >= n) throw Error("key \"" + key + "\" has no value");
+        ++i;
+        std::string val;
+        if (i < n && s[i] == '{') {
+            size_t j = s.find('}', i);
+            if (j == std::string::npos) throw Error("list must terminate with '}'");
+            val = s.substr(i, j + 1 - i);
+            i = j + 1;
+            if (i < n && s[i] == ',') ++i;
+        } else {
+            while (i < n) {
+                if (s[i] == '\\' && i + 1 < n) { val.push_back(s[i + 1]); i += 2; continue; }
+                if (s[i] == ',') { ++i; break; }
+                val.push_back(s[i++]);
+            }
+        }
+        pairs.push_back({key, val});
+    }
+    return pairs;
+}
+
+struct PathElem { bool is_index; std::string key; size_t index; };
+
+std::vector<PathElem> split_key(const std::string &key) {
+    std::vector<PathElem> parts;
+    std::string cur;
+    for (size_t i = 0; i < key.size();) {
+        char c = key[i];
+        if (c == '\\' && i + 1 < key.size()) { cur.push_back(key[i + 1]); i += 2; }
+        else if (c == '.') { if (!cur.empty()) parts.push_back({false, cur, 0}); cur.clear(); ++i; }
+        else if (c == '[') {
+            if (!cur.empty()) parts.push_back({false, cur, 0});
+            cur.clear();
+            size_t j = key.find(']', i);
+            if (j == std::string::npos) throw Error("unterminated index in key " + key);
+            parts.push_back({true, "", (size_t)strtoull(key.substr(i + 1, j - i - 1).c_str(), nullptr, 10)});
+            i = j + 1;
+        } else { cur.push_back(c); ++i; }
+    }
+    if (!cur.empty()) parts.push_back({false, cur, 0});
+    return parts;
+}
+
+void assign(Value &root, const std::vector<PathElem> &path, const Value &value) {
+    if (root.kind != Value::MapK) root = Value::make_map();
+    Value *cur = &root;
+    for (size_t k = 0; k < path.size(); ++k) {
+        bool last = k + 1 == path.size();
+        bool next_is_index = !last && path[k + 1].is_index;
+        Value *slot;
+        if (path[k].is_index) {
+            if (cur->kind != Value::ListK) *cur = Value::make_list();
+            while (cur->list->size() <= path[k].index) cur->list->push_back(Value::nil());
+            slot = &(*cur->list)[path[k].index];
+        } else {
+            if (cur->kind != Value::MapK) *cur = Value::make_map();
+            slot = &(*cur->map)[path[k].key];
+        }
+        if (last) { *slot = value; return; }
+        if (slot->kind != Value::MapK && slot->kind != Value::ListK) *slot = next_is_index ? Value::make_list() : Value::make_map();
+        cur = slot;
+    }
+}
+
+}  // namespace
+
+void apply_set(Value &values, const std::string &expr, bool force_string) {
+    for (const auto &kv : split_set(expr)) {
+        const std::string &val = kv.second;
+        Value v;
+        if (val.size() >= 2 && val.front() == '{' && val.back() == '}') {
+            v = Value::make_list();
+            std::string inner = val.substr(1, val.size() - 2);
+            if (!inner.empty()) {
+                size_t i = 0;
+                for (;;) {
+                    size_t j = inner.find(',', i);
+                    std::string item = trim_space(inner.substr(i, j == std::string::npos ? std::string::npos : j - i));
+                    v.list->push_back(set_typed(item, force_string));
+                    if (j == std::string::npos) break;
+                    i = j + 1;
+                }
+            }
+        } else {
+            v = set_typed(val, force_string);
+        }
+        assign(values, split_key(kv.first), v);
+    }
+}
+
+void apply_set_file(Value &values, const std::string &expr) {
+    for (const auto &kv : split_set(expr)) assign(values, split_key(kv.first), Value::str(read_file(kv.second)));
+}
+
+void apply_set_blob(Value &values, const std::string &key, const std::string &content) {
+    assign(values, split_key(key), Value::str(content));
+}
+
+// ============================================================================ chart
+namespace {
+
+struct IgnoreRule { std::string pat; bool neg, dir_only, anchored; };
+
+std::vector<IgnoreRule> ignore_rules(const std::string &text) {
+    std::vector<IgnoreRule> rules;
+    std::istringstream ss(text);
+    std::string line;
+    while (std::getline(ss, line)) {
+        line = trim_space(line);
+        if (line.empty() || line[0] == '#') continue;
+        IgnoreRule r{line, false, false, false};
+        if (r.pat[0] == '!') { r.neg = true; r.pat.erase(0, 1); }
+        if (!r.pat.empty() && r.pat.back() == '/') { r.dir_only = true; r.pat.pop_back(); }
+        if (!r.pat.empty() && r.pat[0] == '/') { r.anchored = true; r.pat.erase(0, 1); }
+        rules.push_back(r);
+    }
+    return rules;
+}
+
+bool ignored(const std::string &rel, bool is_dir, const std::vector<IgnoreRule> &rules) {
+    bool ig = false;
+    std::string base = rel.substr(rel.find_last_of('/') == std::string::npos ? 0 : rel.find_last_of('/') + 1);
+    for (const auto &r : rules) {
+        if (r.dir_only && !is_dir) continue;
+        bool hit = (r.pat.find('/') != std::string::npos || r.anchored) ? fnmatch(r.pat.c_str(), rel.c_str(), 0) == 0
+                                                                        : fnmatch(r.pat.c_str(), base.c_str(), 0) == 0;
+        if (hit) ig = !r.neg;
+    }
+    return ig;
+}
+
+void walk(const std::string &root, const std::string &rel, const std::vector<IgnoreRule> &rules,
+          std::vector<std::pair<std::string, std::string>> *out) {
+    std::string dirpath = root + "/" + rel;
+    DIR *d = opendir(dirpath.c_str());
+    if (!d) return;
+    std::vector<std::string> names;
+    while (struct dirent *e = readdir(d)) {
+        std::string n = e->d_name;
+        if (n != "." && n != "..") names.push_back(n);
+    }
+    closedir(d);
+    std::sort(names.begin(), names.end());
+    for (const auto &n : names) {
+        std::string r = rel + "/" + n;
+        struct stat st;
+        if (stat((root + "/" + r).c_str(), &st) != 0) continue;
+        bool is_dir = S_ISDIR(st.st_mode);
+        if (ignored(r, is_dir, rules)) continue;
+        if (is_dir) walk(root, r, rules, out);
+        else out->push_back({r, read_file(root + "/" + r)});
+    }
+}
+
+}  // namespace
+
+std::string Chart::name() const {
+    if (metadata.kind == Value::MapK) {
+        auto it = metadata.map->find("name");
+        if (it != metadata.map->end()) return tmpl::go_print(it->second);
+    }
+    return "";
+}
+
+Chart load_chart(const std::string &dir) {
+    Chart c;
+    c.dir = dir;
+    c.metadata = parse_yaml(read_file(dir + "/Chart.yaml"), false);
+    if (c.metadata.kind != Value::MapK) throw Error("Chart.yaml: not a mapping");
+    c.values = Value::make_map();
+    if (file_exists(dir + "/values.yaml")) {
+        Value v = parse_yaml(read_file(dir + "/values.yaml"), true);
+        if (v.kind == Value::MapK) c.values = v;
+        else if (!v.is_nilish()) throw Error("values.yaml: not a mapping");
+    }
+    std::vector<IgnoreRule> rules;
+    if (file_exists(dir + "/.helmignore")) rules = ignore_rules(read_file(dir + "/.helmignore"));
+    walk(dir, "templates", rules, &c.templates);
+    return c;
+}
+
+// ============================================================================ manifests
+static const char *kInstallOrder[] = {
+    "Namespace", "NetworkPolicy", "ResourceQuota", "LimitRange", "PodSecurityPolicy", "PodDisruptionBudget",
+    "ServiceAccount", "Secret", "SecretList", "ConfigMap", "StorageClass", "PersistentVolume",
+    "PersistentVolumeClaim", "CustomResourceDefinition", "ClusterRole", "ClusterRoleList",
+    "ClusterRoleBinding", "ClusterRoleBindingList", "Role", "RoleList", "RoleBinding", "RoleBindingList",
+    "Service", "DaemonSet", "Pod", "ReplicationController", "ReplicaSet", "Deployment",
+    "HorizontalPodAutoscaler", "StatefulSet", "Job", "CronJob", "Ingress", "APIService"};
+
+static int install_rank(const std::string &kind) {
+    for (size_t i = 0; i < sizeof kInstallOrder / sizeof *kInstallOrder; ++i)
+        if (kind == kInstallOrder[i]) return (int)i;
+    return -1;
+}
+
+// Split on lines that are "---" followed only by white space (Go: (?m)^---\s*$).
+static std::vector<std::string> split_docs(const std::string &s) {
+    std::vector<std::string> docs;
+    size_t start = 0, i = 0;
+    while (i <= s.size()) {
+        size_t j = s.find('\n', i);
+        if (j == std::string::npos) j = s.size();
+        bool sep = s.compare(i, 3, "---") == 0;
+        if (sep)
+            for (size_t k = i + 3; k < j; ++k)
+                if (!is_ws(s[k])) sep = false;
+        if (sep) {
+            docs.push_back(s.substr(start, i - start));
+            start = j < s.size() ? j + 1 : j;
+        }
+        i = j + 1;
+    }
+    docs.push_back(start <= s.size() ? s.substr(start) : "");
+    return docs;
+}
+
+void split_manifests(const std::map<std::string, std::string> &files, std::vector<Manifest> *out, std::string *notes) {
+    out->clear();
+    notes->clear();
+    for (const auto &kv : files) {  // std::map: sorted by path, like Helm sorts file names
+        const std::string &name = kv.first;
+        std::string base = name.substr(name.find_last_of('/') + 1);
+        if (base == "NOTES.txt") { *notes = kv.second; continue; }
+        std::string t = trim_space(kv.second);
+        if (t.empty()) continue;
+        for (std::string doc : split_docs(t)) {
+            size_t a = 0;
+            while (a < doc.size() && is_ws(doc[a])) ++a;
+            doc.erase(0, a);
+            if (doc.empty()) continue;
+            // top-level "kind:" of the document head
+            std::string kind;
+            size_t i = 0;
+            while (i < doc.size()) {
+                size_t j = doc.find('\n', i);
+                if (j == std::string::npos) j = doc.size();
+                if (doc.compare(i, 5, "kind:") == 0) {
+                    size_t k = i + 5;
+                    while (k < j && (doc[k] == ' ' || doc[k] == '\t')) ++k;
+                    size_t e = k;
+                    while (e < j && !is_ws(doc[e]) && doc[e] != '#') ++e;
+                    kind = doc.substr(k, e - k);
+                    if (kind.size() >= 2 && (kind.front() == '"' || kind.front() == '\'')) kind = kind.substr(1, kind.size() - 2);
+                    break;
+                }
+                i = j + 1;
+            }
+            out->push_back({name, kind, doc});
+        }
+    }
+    std::stable_sort(out->begin(), out->end(), [](const Manifest &a, const Manifest &b) {
+        int ra = install_rank(a.kind), rb = install_rank(b.kind);
+        if (ra < 0 && rb < 0) return a.kind < b.kind;  // unknown kinds: alphabetical, stable within a kind
+        if (ra < 0) return false;
+        if (rb < 0) return true;
+        return ra < rb;
+    });
+}
+
+}  // namespace chart
+}  // namespace kvedge

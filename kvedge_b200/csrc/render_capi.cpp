@@ -1,0 +1,524 @@
+// extern "C" render entry points (declared in include/kvedge_b200.h): load a chart, plan a
+// release (render with every top-level `| b64enc` site left pending), encode the pending
+// Secret payloads on the GPU in one batch, and frame the result like `helm template`.
+//
+// Reference path: README.md:60 (`helm install ... --set ... --set-file azIotEdgeConfig=...`)
+// -> deployment/helm/templates/* -> the two b64enc sites
+// (aziot-edge-runtime-config-secret.yaml:6, aziot-edge-vm-cloud-init-secret.yaml:6).
+#include "../../include/kvedge_b200.h"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "chart.hpp"
+#include "tmpl.hpp"
+
+using kvedge::chart::Chart;
+using kvedge::chart::Manifest;
+using kvedge::tmpl::Pending;
+using kvedge::tmpl::TemplateSet;
+using kvedge::tmpl::Value;
+
+extern "C" int kv_set_last_error_(int code, const char *msg);  // capi.cu
+
+struct kv_chart {
+    Chart chart;
+    TemplateSet ts;
+    bool templates_have_sentinels = false;
+};
+
+struct kv_release {
+    std::string manifest;           // helm-template framed stream (placeholders while pending)
+    std::string notes;
+    std::vector<Pending> pending;
+    std::vector<std::string> filled;  // encoded text per pending site ("" until filled)
+    size_t n_filled = 0;
+    bool spliced = false;
+};
+
+namespace {
+
+int fail(int code, const std::string &msg) { return kv_set_last_error_(code, msg.c_str()); }
+
+Value chart_struct(const Value &meta) {
+    Value s = Value::make_struct("chart.Metadata");
+    auto get = [&](const char *k, Value d) -> Value {
+        auto it = meta.map->find(k);
+        if (it == meta.map->end() || it->second.is_nilish()) return d;
+        return it->second;
+    };
+    auto str_of = [&](const char *k) { return Value::str(kvedge::tmpl::go_print(get(k, Value::str("")))); };
+    (*s.map)["Name"] = get("name", Value::str(""));
+    (*s.map)["Home"] = get("home", Value::str(""));
+    (*s.map)["Sources"] = get("sources", Value::make_list());
+    (*s.map)["Version"] = str_of("version");
+    (*s.map)["Description"] = get("description", Value::str(""));
+    (*s.map)["Keywords"] = get("keywords", Value::make_list());
+    (*s.map)["Maintainers"] = get("maintainers", Value::make_list());
+    (*s.map)["Icon"] = get("icon", Value::str(""));
+    (*s.map)["APIVersion"] = get("apiVersion", Value::str(""));
+    (*s.map)["Condition"] = get("condition", Value::str(""));
+    (*s.map)["Tags"] = get("tags", Value::str(""));
+    (*s.map)["AppVersion"] = str_of("appVersion");
+    (*s.map)["Deprecated"] = Value::boolean(kvedge::tmpl::truth(get("deprecated", Value::boolean(false))));
+    (*s.map)["Annotations"] = get("annotations", Value::make_map());
+    (*s.map)["KubeVersion"] = get("kubeVersion", Value::str(""));
+    (*s.map)["Dependencies"] = get("dependencies", Value::make_list());
+    (*s.map)["Type"] = get("type", Value::str(""));
+    return s;
+}
+
+bool value_has_sentinels(const Value &v) {
+    if (v.kind == Value::String) return TemplateSet::has_sentinel_bytes(v.s);
+    if (v.list)
+        for (const auto &x : *v.list)
+            if (value_has_sentinels(x)) return true;
+    if (v.map)
+        for (const auto &kv : *v.map)
+            if (TemplateSet::has_sentinel_bytes(kv.first) || value_has_sentinels(kv.second)) return true;
+    return false;
+}
+
+void replace_all_inplace(std::string &s, const std::string &from, const std::string &to) {
+    size_t i = 0;
+    while ((i = s.find(from, i)) != std::string::npos) {
+        s.replace(i, from.size(), to);
+        i += to.size();
+    }
+}
+
+std::string gpu_encode_one(const std::string &in) {
+    std::string out(kv_b64enc_len(in.size()), '\0');
+    int rc = kv_b64enc(reinterpret_cast<const uint8_t *>(in.data()), in.size(), &out[0]);
+    if (rc != KV_OK) throw kvedge::tmpl::Error(std::string("b64enc: ") + kv_last_error());
+    return out;
+}
+
+std::string gpu_decode_one(const std::string &in) {
+    std::string out(kv_b64dec_maxlen(in.size()) + 4, '\0');
+    size_t n = 0, eo = 0;
+    int rc = kv_b64dec(in.data(), in.size(), reinterpret_cast<uint8_t *>(&out[0]), &n, &eo);
+    if (rc == KV_ECORRUPT) return std::string("illegal base64 data at input byte ") + std::to_string(eo);
+    if (rc != KV_OK) throw kvedge::tmpl::Error(std::string("b64dec: ") + kv_last_error());
+    out.resize(n);
+    return out;
+}
+
+Value merged_values(const kv_chart *c, const kv_overrides *ov) {
+    Value vals = kvedge::tmpl::deep_copy(c->chart.values);
+    if (!ov) return vals;
+    for (int i = 0; i < ov->n_set; ++i) kvedge::chart::apply_set(vals, ov->set[i], false);
+    for (int i = 0; i < ov->n_set_string; ++i) kvedge::chart::apply_set(vals, ov->set_string[i], true);
+    for (int i = 0; i < ov->n_set_file; ++i) kvedge::chart::apply_set_file(vals, ov->set_file[i]);
+    for (int i = 0; i < ov->n_blob; ++i)
+        kvedge::chart::apply_set_blob(vals, ov->blob_keys[i],
+                                      std::string(reinterpret_cast<const char *>(ov->blob_data[i]), ov->blob_len[i]));
+    return vals;
+}
+
+// Render every non-partial file of the chart; keys are "<chart>/templates/<file>".
+std::map<std::string, std::string> render_files(const kv_chart *c, const Value &vals, const char *release,
+                                                const char *ns, bool defer, std::vector<Pending> *pending) {
+    const std::string prefix = c->chart.name() + "/";
+    Value rel = Value::make_map();
+    (*rel.map)["Name"] = Value::str(release ? release : "release-name");
+    (*rel.map)["Namespace"] = Value::str(ns ? ns : "default");
+    (*rel.map)["IsUpgrade"] = Value::boolean(false);
+    (*rel.map)["IsInstall"] = Value::boolean(true);
+    (*rel.map)["Revision"] = Value::integer(1);
+    (*rel.map)["Service"] = Value::str("Helm");
+    Value caps = Value::make_map();
+    Value kube = Value::make_map();
+    (*kube.map)["Version"] = Value::str("v1.20.0");
+    (*kube.map)["Major"] = Value::str("1");
+    (*kube.map)["Minor"] = Value::str("20");
+    (*caps.map)["KubeVersion"] = kube;
+    Value hv = Value::make_map();
+    (*hv.map)["Version"] = Value::str("v3.7.0");
+    (*caps.map)["HelmVersion"] = hv;
+    Value chart_meta = chart_struct(c->chart.metadata);
+
+    TemplateSet::ExecOptions opt;
+    opt.defer_b64 = defer;
+    opt.pending = pending;
+    opt.encode = gpu_encode_one;
+    opt.decode = gpu_decode_one;
+    std::map<std::string, std::string> out;
+    for (const auto &t : c->chart.templates) {
+        const std::string &rel_path = t.first;
+        std::string base = rel_path.substr(rel_path.find_last_of('/') + 1);
+        if (!base.empty() && base[0] == '_') continue;
+        Value top = Value::make_map();
+        (*top.map)["Values"] = vals;
+        (*top.map)["Chart"] = chart_meta;
+        (*top.map)["Release"] = rel;
+        Value tv = Value::make_map();
+        (*tv.map)["Name"] = Value::str(prefix + rel_path);
+        (*tv.map)["BasePath"] = Value::str(prefix + "templates");
+        (*top.map)["Template"] = tv;
+        (*top.map)["Capabilities"] = caps;
+        std::string rendered;
+        try {
+            rendered = c->ts.execute(prefix + rel_path, top, opt);
+        } catch (const kvedge::tmpl::Error &e) {
+            throw kvedge::tmpl::Error("template: " + prefix + rel_path + ": " + e.what());
+        }
+        replace_all_inplace(rendered, "<no value>", "");  // missingkey=zero, non-strict
+        out[prefix + rel_path] = rendered;
+    }
+    return out;
+}
+
+void frame(const std::map<std::string, std::string> &files, std::string *manifest, std::string *notes) {
+    std::vector<Manifest> ms;
+    std::string raw_notes;
+    kvedge::chart::split_manifests(files, &ms, &raw_notes);
+    manifest->clear();
+    for (const auto &m : ms) *manifest += "---\n# Source: " + m.name + "\n" + m.content + "\n";
+    *notes = kvedge::chart::trim_space(raw_notes);
+}
+
+// Write every filled encoding over its placeholder (found by its 4 id bytes).
+void splice(std::string &text, const std::vector<Pending> &pending, const std::vector<std::string> &filled) {
+    for (size_t i = 0; i + 4 <= text.size();) {
+        unsigned char c = (unsigned char)text[i];
+        if (c >= 0x10 && c < 0x20) {
+            size_t id = 0;
+            for (int k = 0; k < 4; ++k) id = (id << 4) | ((unsigned char)text[i + (size_t)k] & 0xF);
+            if (id < pending.size() && filled[id].size() == pending[id].encoded_len && i + pending[id].encoded_len <= text.size()) {
+                memcpy(&text[i], filled[id].data(), filled[id].size());
+                i += filled[id].size();
+                continue;
+            }
+        }
+        ++i;
+    }
+}
+
+int plan_release(const kv_chart *c, const char *release, const char *ns, const kv_overrides *ov, bool defer,
+                 kv_release **out) {
+    std::unique_ptr<kv_release> r(new kv_release);
+    Value vals = merged_values(c, ov);
+    bool can_defer = defer && !c->templates_have_sentinels && !value_has_sentinels(vals);
+    auto files = render_files(c, vals, release, ns, can_defer, &r->pending);
+    frame(files, &r->manifest, &r->notes);
+    r->filled.assign(r->pending.size(), std::string());
+    *out = r.release();
+    return KV_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int kv_chart_load(const char *chart_dir, kv_chart **out) {
+    if (!chart_dir || !out) return fail(KV_EINVAL, "null argument");
+    try {
+        std::unique_ptr<kv_chart> c(new kv_chart);
+        c->chart = kvedge::chart::load_chart(chart_dir);
+        const std::string prefix = c->chart.name() + "/";
+        for (const auto &t : c->chart.templates) {
+            c->ts.parse(prefix + t.first, t.second);
+            if (TemplateSet::has_sentinel_bytes(t.second)) c->templates_have_sentinels = true;
+        }
+        *out = c.release();
+        return KV_OK;
+    } catch (const std::exception &e) {
+        return fail(KV_ETEMPLATE, e.what());
+    }
+}
+
+void kv_chart_free(kv_chart *c) { delete c; }
+
+int kv_release_plan(const kv_chart *chart, const char *release_name, const char *ns,
+                    const kv_overrides *overrides, kv_release **out) {
+    if (!chart || !out) return fail(KV_EINVAL, "null argument");
+    try {
+        return plan_release(chart, release_name, ns, overrides, true, out);
+    } catch (const std::exception &e) {
+        return fail(KV_ETEMPLATE, e.what());
+    }
+}
+
+int kv_release_pending_count(const kv_release *r) { return r ? (int)r->pending.size() : 0; }
+
+int kv_release_pending_input(const kv_release *r, int i, const uint8_t **data, size_t *len) {
+    if (!r || i < 0 || (size_t)i >= r->pending.size() || !data || !len) return fail(KV_EINVAL, "bad pending index");
+    *data = reinterpret_cast<const uint8_t *>(r->pending[(size_t)i].input.data());
+    *len = r->pending[(size_t)i].input.size();
+    return KV_OK;
+}
+
+int kv_release_pending_fill(kv_release *r, int i, const char *enc, size_t len) {
+    if (!r || i < 0 || (size_t)i >= r->pending.size() || !enc) return fail(KV_EINVAL, "bad pending index");
+    if (len != r->pending[(size_t)i].encoded_len)
+        return fail(KV_EINVAL, "encoded length " + std::to_string(len) + " != " +
+                                   std::to_string(r->pending[(size_t)i].encoded_len));
+    if (r->filled[(size_t)i].empty()) ++r->n_filled;
+    r->filled[(size_t)i].assign(enc, len);
+    r->spliced = false;
+    return KV_OK;
+}
+
+int kv_release_encode_gpu(kv_release *r) {
+    if (!r) return fail(KV_EINVAL, "null release");
+    const size_t n = r->pending.size();
+    if (n == 0) return KV_OK;
+    std::vector<int64_t> in_off(n + 1, 0), out_off(n + 1, 0);
+    for (size_t i = 0; i < n; ++i) {
+        in_off[i + 1] = in_off[i] + (int64_t)r->pending[i].input.size();
+        out_off[i + 1] = out_off[i] + (int64_t)((r->pending[i].encoded_len + 15) / 16 * 16);
+    }
+    std::string blob;
+    blob.reserve((size_t)in_off[n]);
+    for (size_t i = 0; i < n; ++i) blob += r->pending[i].input;
+    std::string enc((size_t)out_off[n], '\0');
+    int rc = kv_b64enc_batch(reinterpret_cast<const uint8_t *>(blob.data()), in_off.data(), (int64_t)n, &enc[0],
+                             out_off.data());
+    if (rc != KV_OK) return rc;
+    for (size_t i = 0; i < n; ++i) r->filled[i].assign(enc, (size_t)out_off[i], r->pending[i].encoded_len);
+    r->n_filled = n;
+    r->spliced = false;
+    return KV_OK;
+}
+
+static int finish(kv_release *r) {
+    if (r->n_filled < r->pending.size())
+        return fail(KV_EINVAL, std::to_string(r->pending.size() - r->n_filled) +
+                                   " b64enc site(s) still pending: call kv_release_encode_gpu first");
+    if (!r->spliced) {
+        splice(r->manifest, r->pending, r->filled);
+        splice(r->notes, r->pending, r->filled);
+        r->spliced = true;
+    }
+    return KV_OK;
+}
+
+int kv_release_manifest(kv_release *r, const char **data, size_t *len) {
+    if (!r || !data || !len) return fail(KV_EINVAL, "null argument");
+    int rc = finish(r);
+    if (rc) return rc;
+    *data = r->manifest.data();
+    *len = r->manifest.size();
+    return KV_OK;
+}
+
+int kv_release_notes(kv_release *r, const char **data, size_t *len) {
+    if (!r || !data || !len) return fail(KV_EINVAL, "null argument");
+    int rc = finish(r);
+    if (rc) return rc;
+    *data = r->notes.data();
+    *len = r->notes.size();
+    return KV_OK;
+}
+
+void kv_release_free(kv_release *r) { delete r; }
+
+int kv_helm_template(const char *chart_dir, const char *release_name, const char *ns,
+                     const kv_overrides *overrides, char **out, size_t *out_len) {
+    if (!out || !out_len) return fail(KV_EINVAL, "null argument");
+    kv_chart *c = nullptr;
+    int rc = kv_chart_load(chart_dir, &c);
+    if (rc) return rc;
+    kv_release *r = nullptr;
+    rc = kv_release_plan(c, release_name, ns, overrides, &r);
+    if (rc == KV_OK) rc = kv_release_encode_gpu(r);
+    const char *data = nullptr;
+    size_t n = 0;
+    if (rc == KV_OK) rc = kv_release_manifest(r, &data, &n);
+    if (rc == KV_OK) {
+        *out = static_cast<char *>(malloc(n + 1));
+        if (!*out) rc = fail(KV_ENOMEM, "malloc");
+        else {
+            memcpy(*out, data, n);
+            (*out)[n] = 0;
+            *out_len = n;
+        }
+    }
+    kv_release_free(r);
+    kv_chart_free(c);
+    return rc;
+}
+
+int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *release_names, const char *ns,
+                      const kv_overrides *overrides, char **out, int64_t *out_off) {
+    if (!chart || n_releases < 0 || !out || !out_off) return fail(KV_EINVAL, "null argument");
+    std::vector<std::unique_ptr<kv_release>> rel((size_t)n_releases);
+    try {
+        for (int i = 0; i < n_releases; ++i) {
+            kv_release *r = nullptr;
+            int rc = plan_release(chart, release_names ? release_names[i] : nullptr, ns,
+                                  overrides ? &overrides[i] : nullptr, true, &r);
+            if (rc) return rc;
+            rel[(size_t)i].reset(r);
+        }
+    } catch (const std::exception &e) {
+        return fail(KV_ETEMPLATE, e.what());
+    }
+    // one packed batch over every pending Secret payload of the fleet
+    std::vector<int64_t> in_off(1, 0), enc_off(1, 0);
+    size_t total_in = 0;
+    for (auto &r : rel)
+        for (auto &p : r->pending) {
+            total_in += p.input.size();
+            in_off.push_back((int64_t)total_in);
+            enc_off.push_back(enc_off.back() + (int64_t)((p.encoded_len + 15) / 16 * 16));
+        }
+    const int64_t n_units = (int64_t)in_off.size() - 1;
+    std::string blob;
+    blob.reserve(total_in);
+    for (auto &r : rel)
+        for (auto &p : r->pending) blob += p.input;
+    std::string enc((size_t)enc_off.back(), '\0');
+    if (n_units > 0) {
+        int rc = kv_b64enc_batch(reinterpret_cast<const uint8_t *>(blob.data()), in_off.data(), n_units, &enc[0],
+                                 enc_off.data());
+        if (rc) return rc;
+    }
+    size_t u = 0, total_out = 0;
+    for (auto &r : rel) {
+        for (size_t i = 0; i < r->pending.size(); ++i, ++u)
+            r->filled[i].assign(enc, (size_t)enc_off[u], r->pending[i].encoded_len);
+        r->n_filled = r->pending.size();
+        splice(r->manifest, r->pending, r->filled);
+        r->spliced = true;
+        total_out += r->manifest.size();
+    }
+    char *buf = static_cast<char *>(malloc(total_out + 1));
+    if (!buf) return fail(KV_ENOMEM, "malloc");
+    size_t pos = 0;
+    for (int i = 0; i < n_releases; ++i) {
+        out_off[i] = (int64_t)pos;
+        memcpy(buf + pos, rel[(size_t)i]->manifest.data(), rel[(size_t)i]->manifest.size());
+        pos += rel[(size_t)i]->manifest.size();
+    }
+    out_off[n_releases] = (int64_t)pos;
+    buf[pos] = 0;
+    *out = buf;
+    return KV_OK;
+}
+
+// ---- lint (BASELINE.json config 1) ------------------------------------------------------
+static bool dns1123(const std::string &s) {
+    if (s.empty() || s.size() > 253) return false;
+    auto alnum = [](char c) { return (c >= 'a' && c <= 'z') || (c >= '0' && c <= '9'); };
+    size_t i = 0;
+    while (i < s.size()) {
+        size_t j = s.find('.', i);
+        if (j == std::string::npos) j = s.size();
+        if (j == i || !alnum(s[i]) || !alnum(s[j - 1])) return false;
+        for (size_t k = i; k < j; ++k)
+            if (!alnum(s[k]) && s[k] != '-') return false;
+        i = j + 1;
+        if (j == s.size()) break;
+        if (i == s.size()) return false;
+    }
+    return true;
+}
+
+static bool semver(const std::string &v) {
+    size_t i = 0;
+    if (i < v.size() && v[i] == 'v') ++i;
+    for (int part = 0; part < 3; ++part) {
+        size_t d0 = i;
+        while (i < v.size() && isdigit((unsigned char)v[i])) ++i;
+        if (i == d0) return false;
+        if (part < 2) {
+            if (i >= v.size() || v[i] != '.') return false;
+            ++i;
+        }
+    }
+    if (i == v.size()) return true;
+    if (v[i] != '-' && v[i] != '+') return false;
+    for (size_t k = i + 1; k < v.size(); ++k)
+        if (!isalnum((unsigned char)v[k]) && v[k] != '.' && v[k] != '-' && v[k] != '+') return false;
+    return i + 1 < v.size();
+}
+
+int kv_helm_lint(const char *chart_dir, const kv_overrides *overrides, int *ok, char **messages, size_t *len) {
+    if (!chart_dir || !ok || !messages || !len) return fail(KV_EINVAL, "null argument");
+    std::vector<std::string> msgs;
+    kv_chart *c = nullptr;
+    if (kv_chart_load(chart_dir, &c) != KV_OK) {
+        msgs.push_back(std::string("[ERROR] Chart.yaml: ") + kv_last_error());
+    } else {
+        const Value &meta = c->chart.metadata;
+        auto get = [&](const char *k) -> std::string {
+            auto it = meta.map->find(k);
+            if (it == meta.map->end() || it->second.is_nilish()) return "";
+            return kvedge::tmpl::go_print(it->second);
+        };
+        if (get("name").empty()) msgs.push_back("[ERROR] Chart.yaml: name is required");
+        std::string api = get("apiVersion");
+        if (api.empty()) msgs.push_back("[ERROR] Chart.yaml: apiVersion is required. The value must be either \"v1\" or \"v2\"");
+        else if (api != "v1" && api != "v2")
+            msgs.push_back("[ERROR] Chart.yaml: apiVersion '" + api + "' is not valid. The value must be either \"v1\" or \"v2\"");
+        std::string ver = get("version");
+        if (ver.empty()) msgs.push_back("[ERROR] Chart.yaml: version is required");
+        else if (!semver(ver)) msgs.push_back("[ERROR] Chart.yaml: version '" + ver + "' is not a valid SemVer");
+        std::string type = get("type");
+        if (!type.empty() && type != "application" && type != "library")
+            msgs.push_back("[ERROR] Chart.yaml: chart type is not valid in apiVersion 'v2'. It must be 'application' or 'library'");
+        if (get("icon").empty()) msgs.push_back("[INFO] Chart.yaml: icon is recommended");
+        try {
+            Value vals = merged_values(c, overrides);
+            std::vector<Pending> pending;
+            bool defer = !c->templates_have_sentinels && !value_has_sentinels(vals);
+            auto files = render_files(c, vals, "test-release", "default", defer, &pending);
+            std::vector<Manifest> ms;
+            std::string notes;
+            kvedge::chart::split_manifests(files, &ms, &notes);
+            std::stable_sort(ms.begin(), ms.end(), [](const Manifest &a, const Manifest &b) { return a.name < b.name; });
+            for (const auto &m : ms) {
+                std::string shortn = m.name.substr(m.name.find('/') + 1);
+                Value doc;
+                try {
+                    doc = kvedge::chart::parse_yaml(m.content, false);
+                } catch (const std::exception &e) {
+                    msgs.push_back("[ERROR] " + shortn + ": unable to parse YAML: " + e.what());
+                    continue;
+                }
+                if (doc.kind != Value::MapK) {
+                    msgs.push_back("[ERROR] " + shortn + ": document is not a mapping");
+                    continue;
+                }
+                for (const char *req : {"apiVersion", "kind"})
+                    if (!doc.map->count(req)) msgs.push_back("[ERROR] " + shortn + ": " + req + " is required");
+                std::string nm;
+                auto md = doc.map->find("metadata");
+                if (md != doc.map->end() && md->second.kind == Value::MapK) {
+                    auto ni = md->second.map->find("name");
+                    if (ni != md->second.map->end() && !ni->second.is_nilish()) nm = kvedge::tmpl::go_print(ni->second);
+                }
+                if (nm.empty()) msgs.push_back("[ERROR] " + shortn + ": object name not present in metadata");
+                else if (!dns1123(nm))
+                    msgs.push_back("[ERROR] " + shortn + ": object name does not conform to Kubernetes naming requirements: \"" + nm + "\"");
+            }
+        } catch (const std::exception &e) {
+            msgs.push_back(std::string("[ERROR] templates/: ") + e.what());
+        }
+        kv_chart_free(c);
+    }
+    *ok = 1;
+    std::string joined;
+    for (const auto &m : msgs) {
+        if (m.compare(0, 7, "[ERROR]") == 0) *ok = 0;
+        joined += m + "\n";
+    }
+    *messages = static_cast<char *>(malloc(joined.size() + 1));
+    if (!*messages) return fail(KV_ENOMEM, "malloc");
+    memcpy(*messages, joined.data(), joined.size());
+    (*messages)[joined.size()] = 0;
+    *len = joined.size();
+    return KV_OK;
+}
+
+void kv_free(void *p) { free(p); }
+
+}  // extern "C"

@@ -1,0 +1,159 @@
+"""Host logic of the render path, no GPU needed: the C++ engine behind the C ABI plans a
+release (b64enc sites pending), the test fills the pending sites with the CPU checker's
+encodings, and the spliced stream must equal the oracle's render byte for byte."""
+import hashlib
+import os
+
+import pytest
+from hypothesis import given, settings, strategies as st
+
+from kvedge_b200 import helm, workload
+from oracle import b64 as ob64
+from oracle import helmref
+
+from conftest import REF_CHART, ROOT
+
+FIXTURE = os.path.join(ROOT, "tests", "fixtures", "edgevm")
+
+
+def _plan_and_fill(chart_dir, release="release-name", **kw):
+    r = helm.Chart(chart_dir).plan(release, **kw)
+    for i, p in enumerate(r.pending):
+        r.fill(i, ob64.encode(p))
+    return r
+
+
+def test_fixture_chart_matches_oracle():
+    sets = ["runtimeConfig=hello world,sshKey=ssh-rsa AAAA+/= u@h", "extraLabels.team=iot,ports[0].port=2222"]
+    r = _plan_and_fill(FIXTURE, "rel1", set=sets)
+    ref = helmref.helm_template(FIXTURE, "rel1", set_args=sets)
+    assert r.manifest() == ref
+    assert r.notes() == helmref.helm_notes(FIXTURE, "rel1", set_args=sets)
+    assert b'big: "1.234567e+06"' in ref          # values.yaml ints are float64 in Helm
+    assert b"disabled-extra" not in ref           # .helmignore glob
+
+
+def test_fixture_pending_sites_are_the_b64enc_inputs():
+    cfg = workload.config_toml(3)
+    r = helm.Chart(FIXTURE).plan("rel2", blobs={"runtimeConfig": cfg})
+    pend = r.pending
+    assert pend[0] == cfg                                   # --set-file content passes verbatim
+    assert pend[1].startswith(b"#cloud-config\nhostname: edgevm\n")
+    with pytest.raises(helm.KvError, match="still pending"):
+        r.manifest()
+    with pytest.raises(helm.KvError, match="encoded length"):
+        r.fill(0, b"AAAA")
+
+
+def test_empty_b64enc_input_is_not_deferred():
+    r = helm.Chart(FIXTURE).plan("rel3")
+    assert len(r.pending) == 1          # runtimeConfig == "" encodes to "" on the spot
+    r.fill(0, ob64.encode(r.pending[0]))
+    assert b"  userdata: \n" in r.manifest()
+
+
+def test_set_file_from_disk_and_binary_payload(tmp_path):
+    raw = bytes(c for c in workload.named_inputs(0)["f4"] if c != 1 and not 0x10 <= c < 0x20)
+    p = tmp_path / "config.bin"
+    p.write_bytes(raw)
+    r = _plan_and_fill(FIXTURE, "rel4", set_file=[f"runtimeConfig={p}"])
+    ref = helmref.helm_template(FIXTURE, "rel4", set_file_args=[f"runtimeConfig={p}"])
+    assert r.manifest() == ref
+    ud = helmref.secret_userdata(r.manifest(), "edgevm-config")
+    assert ob64.decode(ud) == raw
+
+
+def test_values_containing_placeholder_bytes_disable_deferral():
+    # control bytes that collide with the placeholder protocol force immediate evaluation,
+    # which needs the GPU: without one the engine must fail loudly, never guess
+    from kvedge_b200 import _lib
+    if _lib.lib().kv_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(helm.TemplateError, match="no CPU fallback"):
+        helm.Chart(FIXTURE).plan("rel5", blobs={"runtimeConfig": b"\x01\x10binary"})
+
+
+def test_template_errors_surface_like_helm(tmp_path):
+    d = tmp_path / "t"
+    (d / "templates").mkdir(parents=True)
+    (d / "Chart.yaml").write_text("apiVersion: v2\nname: t\nversion: 0.1.0\n")
+    (d / "values.yaml").write_text("flag: true\n")
+    (d / "templates" / "a.yaml").write_text("{{ if eq .Values.flag true }}x: 1{{ end }}\n")
+    assert helm.Chart(str(d)).plan("r").manifest() == b"---\n# Source: t/templates/a.yaml\nx: 1\n"
+    with pytest.raises(helm.TemplateError, match="incompatible types"):
+        helm.Chart(str(d)).plan("r", set_string=["flag=true"])     # eq bool vs string, as in Helm
+    (d / "templates" / "b.yaml").write_text("{{ .Values.a.b }}\n")
+    with pytest.raises(helm.TemplateError, match="nil pointer"):
+        helm.Chart(str(d)).plan("r")
+    (d / "templates" / "b.yaml").write_text("{{ if }}\n")
+    with pytest.raises(helm.TemplateError):
+        helm.Chart(str(d))
+
+
+def test_lint_fixture_and_broken_chart(tmp_path):
+    assert helm.lint(FIXTURE) == helmref.helm_lint(FIXTURE) == (True, [])
+    d = tmp_path / "bad"
+    (d / "templates").mkdir(parents=True)
+    (d / "Chart.yaml").write_text("apiVersion: v9\nname: bad\nversion: one\n")
+    (d / "templates" / "a.yaml").write_text("apiVersion: v1\nkind: ConfigMap\nmetadata:\n  name: Not_Valid\n")
+    ok, msgs = helm.lint(str(d))
+    assert (ok, msgs) == helmref.helm_lint(str(d))
+    assert not ok and any("SemVer" in m for m in msgs) and any("naming" in m for m in msgs)
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.text(alphabet=st.characters(min_codepoint=32, max_codepoint=126, blacklist_characters=",\\{}[]="), max_size=60),
+       st.binary(max_size=300))
+def test_property_engines_agree_on_random_overrides(name, payload):
+    payload = bytes(c for c in payload if c != 1 and not (0x10 <= c < 0x20))
+    sets = [f"nameOverride={name}"]
+    r = helm.Chart(FIXTURE).plan("p", set=sets, blobs={"sshKey": payload})
+    # oracle side: inject the same blob through its values API
+    ch = helmref.load_chart(FIXTURE)
+    vals = helmref.render_values(ch, sets)
+    helmref._assign(vals, ["sshKey"], payload)
+    ms, _ = helmref.split_manifests(helmref.render_files(ch, vals, "p"))
+    ref = b"".join(b"---\n# Source: " + m.name.encode() + b"\n" + m.content + b"\n" for m in ms)
+    for i, p in enumerate(r.pending):
+        r.fill(i, ob64.encode(p))
+    assert r.manifest() == ref
+
+
+# ---- the reference chart itself (build container only) -------------------------------------
+@pytest.mark.needs_reference
+def test_reference_chart_config1_matches_oracle_and_golden(golden_chart):
+    r = _plan_and_fill(REF_CHART)
+    m = r.manifest()
+    assert m == helmref.helm_template(REF_CHART)
+    g = golden_chart["config1"]
+    assert len(m) == g["stream_len"] and hashlib.sha256(m).hexdigest() == g["stream_sha256"]
+    assert len(r.pending) == 1 and hashlib.sha256(r.pending[0]).hexdigest() == g["cloudinit_default_payload_sha256"]
+    assert helm.lint(REF_CHART) == (golden_chart["lint"]["ok"], golden_chart["lint"]["messages"])
+
+
+@pytest.mark.needs_reference
+def test_reference_chart_config2_matches_golden(golden_chart, tmp_path):
+    g = golden_chart["config2"]
+    cfg = workload.config_toml(g["config_toml_seed"])
+    p = tmp_path / "config.toml"
+    p.write_bytes(cfg)
+    r = _plan_and_fill(REF_CHART, set=[g["set"]], set_file=[f"azIotEdgeConfig={p}"])
+    m = r.manifest()
+    assert hashlib.sha256(m).hexdigest() == g["stream_sha256"] and len(m) == g["stream_len"]
+    assert r.pending[0] == cfg                      # a1: the file's bytes, verbatim (values.yaml:14)
+    assert r.pending[1].startswith(b"#cloud-config\nhostname: iotedgevm\n")   # a3: _helper.tpl:31-75
+    assert r.pending[1].endswith(b"sudo iotedge config apply")
+
+
+@pytest.mark.needs_reference
+def test_reference_notes_equal_cast2294(golden_chart):
+    r = _plan_and_fill(REF_CHART, golden_chart["release_name_cast2294"], set=["nameOverride=aziot-edge-kubevirt"])
+    assert r.notes().decode() == golden_chart["notes_cast2294"]
+
+
+@pytest.mark.needs_reference
+def test_reference_name_helper_edge_cases():
+    for override in ["a" * 39 + "-bcdef", "", "x-", "-" * 45, "é" * 25]:
+        sets = [f"nameOverride={override}"]
+        r = _plan_and_fill(REF_CHART, set=sets)
+        assert r.manifest() == helmref.helm_template(REF_CHART, set_args=sets), override
