@@ -206,9 +206,9 @@ __device__ __forceinline__ void store_chars(char *dst, uint4 v, int nchars) {
     }
 }
 
-// Edge thread: the unit's tail (fewer than 12 bytes, '=' padding) or a thread whose
-// word loads would leave the blob.  Byte loads, byte stores.
-__device__ __noinline__ void encode_edge(const uint8_t *p, char *q, int nvalid) {
+// Byte-wise path for the rare tiles whose word loads could leave the blob (its very
+// first and last bytes) or whose destination is not even 4-byte aligned.
+__device__ __noinline__ void encode_bytes(const uint8_t *p, char *q, int nvalid) {
     uint32_t a[3] = {0u, 0u, 0u};
 #pragma unroll
     for (int i = 0; i < 12; ++i)
@@ -227,63 +227,79 @@ __device__ __noinline__ void encode_edge(const uint8_t *p, char *q, int nvalid) 
     store_chars(q, v, (nvalid + 2) / 3 * 4);
 }
 
-constexpr int kEncRows = kEncTileIn / (kThreads * 12);
-
-// All rows of one tile.  SHIFTED: the tile's first byte is not 4-byte aligned, so each
-// thread loads one more word and funnel-shifts.  STORE: 0 = 16-byte aligned destination
-// (one STG.128 per thread), 1 = 4-byte aligned (four STG.32), 2 = unaligned (bytes).
-// `fast_len` is `len` when word loads anywhere in the tile stay inside the blob, else 0.
-template <bool SHIFTED, int STORE>
-__device__ __forceinline__ void encode_tile_rows(const uint8_t *src, char *dst, int len,
-                                                 int fast_len, uint32_t sh) {
-    const uint32_t *wbase = reinterpret_cast<const uint32_t *>(src - sh) + threadIdx.x * 3;
+// One tile, one warp: lane l of iteration i takes input bytes [384 i + 12 l, +12) and
+// writes output bytes [512 i + 16 l, +16), so a warp reads 384 contiguous bytes and
+// stores 512 contiguous bytes per iteration.
+//   SHIFTED  the tile's first byte is not 4-byte aligned: one more word per lane and
+//            a funnel shift (the shift amount is uniform over the tile);
+//   VEC16    the destination is 16-byte aligned: one STG.128 per lane, else four STG.32.
+// The unit's last lane (fewer than 12 bytes left) masks the bytes that are not its own,
+// patches in the '=' padding and stores only its 4, 8 or 12 characters.
+template <bool SHIFTED, bool VEC16>
+__device__ __forceinline__ void encode_tile_warp(const uint8_t *src, char *dst, int len,
+                                                 uint32_t sh, int lane) {
+    const uint32_t *wp = reinterpret_cast<const uint32_t *>(src - sh) + lane * 3;
+    char *q = dst + lane * 16;
     const uint32_t s8 = sh * 8;
-#pragma unroll
-    for (int row = 0; row < kEncRows; ++row) {
-        const int off = row * (kThreads * 12) + (int)threadIdx.x * 12;
-        char *q = dst + (row * (kThreads * 16) + (int)threadIdx.x * 16);
-        if (off + 12 <= fast_len) {
-            const uint32_t *wp = wbase + row * (kThreads * 3);
-            uint32_t a0 = __ldg(wp), a1 = __ldg(wp + 1), a2 = __ldg(wp + 2);
-            if (SHIFTED) {
-                const uint32_t a3 = __ldg(wp + 3);
-                a0 = __funnelshift_r(a0, a1, s8);
-                a1 = __funnelshift_r(a1, a2, s8);
-                a2 = __funnelshift_r(a2, a3, s8);
-            }
+    for (int off = lane * 12; off < len; off += 384, wp += 96, q += 512) {
+        uint32_t a0 = __ldg(wp), a1 = __ldg(wp + 1), a2 = __ldg(wp + 2);
+        if (SHIFTED) {
+            const uint32_t a3 = __ldg(wp + 3);
+            a0 = __funnelshift_r(a0, a1, s8);
+            a1 = __funnelshift_r(a1, a2, s8);
+            a2 = __funnelshift_r(a2, a3, s8);
+        }
+        const int left = len - off;
+        if (left >= 12) {
             const uint4 v = encode12(a0, a1, a2);
-            if (STORE == 0) {
+            if (VEC16) {
                 *reinterpret_cast<uint4 *>(q) = v;
-            } else if (STORE == 1) {
+            } else {
                 uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
                 q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
-            } else {
-                store_chars(q, v, 16);
             }
-        } else if (off < len) {
-            encode_edge(src + off, q, (len - off) < 12 ? (len - off) : 12);
         } else {
-            break;
+            // tail of the unit: 1..11 bytes are ours, the rest of the words is not
+            const uint32_t keep = 0xFFFFFFFFu >> (8 * (3 - ((left - 1) & 3)));
+            if (left <= 4) { a0 &= keep; a1 = 0u; a2 = 0u; }
+            else if (left <= 8) { a1 &= keep; a2 = 0u; }
+            else { a2 &= keep; }
+            const uint4 v = encode12(a0, a1, a2);
+            uint32_t w[4] = {v.x, v.y, v.z, v.w};
+            const int rem = left % 3, gi = left / 3;
+            if (rem) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g)
+                    if (g == gi)
+                        w[g] = (rem == 1) ? ((w[g] & 0x0000FFFFu) | 0x3D3D0000u)
+                                          : ((w[g] & 0x00FFFFFFu) | 0x3D000000u);
+            }
+            const int nwords = (left + 2) / 3;
+            uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+                if (g < nwords) q4[g] = w[g];
         }
     }
 }
 
-// Persistent grid; blocks pull tiles from a counter in the scratch header so that ragged
-// units (an 11 KiB config next to a 2.4 KB cloud-init text) cannot pile up on some SMs.
-// header: [0] n_tiles, [1] next tile, [2] blocks finished (the last one re-arms [1],[2]).
+// Persistent grid of independent warps: each warp pulls whole tiles (one contiguous piece
+// of one unit, at most 12 KiB) from a counter in the scratch header, so ragged units -- an
+// 11 KiB config next to a 2.4 KB cloud-init text -- spread evenly and no block-wide
+// barrier is ever needed.  header: [0] n_tiles, [1] next tile, [2] warps finished (the
+// last one re-arms [1] and [2] for the next launch over the same plan).
 __global__ void __launch_bounds__(kThreads, 8)
 b64enc_tiles(const uint8_t *__restrict__ in, char *__restrict__ out,
              const TileDesc *__restrict__ desc, int *__restrict__ header,
              const int64_t *__restrict__ in_off, int64_t n_units) {
-    __shared__ int s_tile[2];
+    const int lane = threadIdx.x & 31;
+    const int n_warps = (int)(gridDim.x * (kThreads / 32));
     const int n_tiles = header[0];
     const int64_t in_end = in_off[n_units];
-    if (threadIdx.x == 0) s_tile[0] = atomicAdd(&header[1], 1);
-    __syncthreads();
-    int tile = s_tile[0];
-    for (int it = 0; tile < n_tiles; ++it) {
+    int tile = (int)(blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5));  // first tile: static
+    while (tile < n_tiles) {
         int next = 0;
-        if (threadIdx.x == 0) next = atomicAdd(&header[1], 1);  // in flight during the tile
+        if (lane == 0) next = atomicAdd(&header[1], 1) + n_warps;  // in flight during the tile
         const int4 *dp = reinterpret_cast<const int4 *>(desc + tile);
         const int4 d0 = __ldg(dp), d1 = __ldg(dp + 1);
         const int64_t in_pos = ((int64_t)(uint32_t)d0.y << 32) | (uint32_t)d0.x;
@@ -293,26 +309,26 @@ b64enc_tiles(const uint8_t *__restrict__ in, char *__restrict__ out,
         char *dst = out + out_pos;
         const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 3u);
         const uint32_t dalign = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
-        // Word loads touch up to 3 bytes before and 4 after a thread's 12 bytes: only take
+        // Word loads touch up to 3 bytes before and 4 after a lane's 12 bytes: only take
         // the word path when that stays inside the blob for the whole tile.
-        const int fast_len = (in_pos >= 3 && in_pos + len + 4 <= in_end) ? len : 0;
-        if (dalign == 0) {
-            if (sh == 0) encode_tile_rows<false, 0>(src, dst, len, fast_len, sh);
-            else encode_tile_rows<true, 0>(src, dst, len, fast_len, sh);
-        } else if ((dalign & 3u) == 0) {
-            if (sh == 0) encode_tile_rows<false, 1>(src, dst, len, fast_len, sh);
-            else encode_tile_rows<true, 1>(src, dst, len, fast_len, sh);
+        const bool words_ok = in_pos >= 3 && in_pos + len + 4 <= in_end && (dalign & 3u) == 0;
+        if (words_ok) {
+            if (dalign == 0) {
+                if (sh == 0) encode_tile_warp<false, true>(src, dst, len, sh, lane);
+                else encode_tile_warp<true, true>(src, dst, len, sh, lane);
+            } else {
+                if (sh == 0) encode_tile_warp<false, false>(src, dst, len, sh, lane);
+                else encode_tile_warp<true, false>(src, dst, len, sh, lane);
+            }
         } else {
-            if (sh == 0) encode_tile_rows<false, 2>(src, dst, len, fast_len, sh);
-            else encode_tile_rows<true, 2>(src, dst, len, fast_len, sh);
+            for (int off = lane * 12; off < len; off += 384)
+                encode_bytes(src + off, dst + off / 3 * 4, (len - off) < 12 ? (len - off) : 12);
         }
-        if (threadIdx.x == 0) s_tile[(it + 1) & 1] = next;
-        __syncthreads();
-        tile = s_tile[(it + 1) & 1];
+        tile = __shfl_sync(0xffffffffu, next, 0);
     }
-    if (threadIdx.x == 0) {
+    if (lane == 0) {
         __threadfence();
-        if (atomicAdd(&header[2], 1) == (int)gridDim.x - 1) {
+        if (atomicAdd(&header[2], 1) == n_warps - 1) {
             header[1] = 0;
             header[2] = 0;
             __threadfence();
