@@ -19,6 +19,8 @@
 //   b64dec_slow              ... and re-decoded sequentially with Go's exact semantics
 #include "b64_kernels.cuh"
 
+#include <cstdlib>
+
 namespace kvedge {
 
 // ----------------------------------------------------------------------------- layout
@@ -186,7 +188,45 @@ __device__ __forceinline__ uint32_t encode_group(uint32_t np) {
     return r;
 }
 
-// 12 input bytes in three little-endian words -> 16 output characters.
+// The same group through a 4096-entry shared-memory table of character pairs (12 input
+// bits -> 2 characters).  Costs two LDS and six ALU operations instead of thirteen ALU
+// operations: the kernel is ALU-pipe bound while the load/store pipe idles, so moving
+// part of the work there shortens the critical pipe.
+__device__ __forceinline__ uint32_t encode_group_lut(uint32_t np, const uint16_t *lut) {
+    const uint32_t ihi = (np >> 19) & 0x1FFEu;  // byte offset of pair (v0, v1)
+    const uint32_t ilo = (np >> 7) & 0x1FFEu;   // byte offset of pair (v2, v3)
+    const uint32_t c01 = *reinterpret_cast<const uint16_t *>(reinterpret_cast<const char *>(lut) + ihi);
+    const uint32_t c23 = *reinterpret_cast<const uint16_t *>(reinterpret_cast<const char *>(lut) + ilo);
+    return __byte_perm(c01, c23, 0x5410);
+}
+
+// Fill the pair table: entry (v0<<6 | v1) = char(v0) | char(v1) << 8.
+__device__ __forceinline__ void fill_pair_lut(uint16_t *lut) {
+    for (int i = threadIdx.x; i < 4096; i += blockDim.x) {
+        // both sextets through the arithmetic mapping (lanes 0 and 1 of one group)
+        const uint32_t np = ((uint32_t)i) << 20;  // v0 = i>>6, v1 = i&63, v2 = v3 = 0
+        lut[i] = (uint16_t)(encode_group(np) & 0xFFFFu);
+    }
+}
+
+// 12 input bytes in three little-endian words -> 16 output characters.  NLUT of the four
+// groups go through the pair table, the others through the arithmetic mapping.
+template <int NLUT>
+__device__ __forceinline__ uint4 encode12_mixed(uint32_t a0, uint32_t a1, uint32_t a2, const uint16_t *lut) {
+    uint4 r;
+    if (NLUT < 0) {  // diagnostic skeleton (tools/sweep_enc.py): memory traffic only, wrong bytes
+        r.x = a0; r.y = a1; r.z = a2; r.w = a0 ^ a2;
+        return r;
+    }
+    const uint32_t g0 = __byte_perm(a0, 0u, 0x0124), g1 = __byte_perm(a0, a1, 0x3455);
+    const uint32_t g2 = __byte_perm(a1, a2, 0x2344), g3 = __byte_perm(a2, 0u, 0x1233);
+    r.x = encode_group(g0);
+    r.y = NLUT >= 1 ? encode_group_lut(g1, lut) : encode_group(g1);
+    r.z = NLUT >= 3 ? encode_group_lut(g2, lut) : encode_group(g2);
+    r.w = NLUT >= 2 ? encode_group_lut(g3, lut) : encode_group(g3);
+    return r;
+}
+
 __device__ __forceinline__ uint4 encode12(uint32_t a0, uint32_t a1, uint32_t a2) {
     uint4 r;
     r.x = encode_group(__byte_perm(a0, 0u, 0x0124));
@@ -235,23 +275,57 @@ __device__ __noinline__ void encode_bytes(const uint8_t *p, char *q, int nvalid)
 //   VEC16    the destination is 16-byte aligned: one STG.128 per lane, else four STG.32.
 // The unit's last lane (fewer than 12 bytes left) masks the bytes that are not its own,
 // patches in the '=' padding and stores only its 4, 8 or 12 characters.
-template <bool SHIFTED, bool VEC16>
+template <bool SHIFTED, bool VEC16, bool PIPE, int NLUT>
 __device__ __forceinline__ void encode_tile_warp(const uint8_t *src, char *dst, int len,
-                                                 uint32_t sh, int lane) {
+                                                 uint32_t sh, int lane, const uint16_t *lut) {
+    if (NLUT == -2) {
+        // diagnostic skeleton 2: fully coalesced 16-byte loads (24 lanes cover the 384 input
+        // bytes of an iteration), 16-byte stores, no arithmetic; bytes are wrong on purpose
+        const uint4 *vp = reinterpret_cast<const uint4 *>(src - (reinterpret_cast<uintptr_t>(src) & 15)) + lane;
+        char *q2 = dst + lane * 16;
+        uint4 nv = make_uint4(0, 0, 0, 0);
+        if (lane < 24) nv = __ldg(vp);
+        for (int o = 0; o < len; o += 384, q2 += 512) {
+            const uint4 v = nv;
+            vp += 24;
+            if (o + 384 < len && lane < 24) nv = __ldg(vp);
+            if (o + lane * 12 + 12 <= len) *reinterpret_cast<uint4 *>(q2) = v;
+        }
+        return;
+    }
     const uint32_t *wp = reinterpret_cast<const uint32_t *>(src - sh) + lane * 3;
     char *q = dst + lane * 16;
     const uint32_t s8 = sh * 8;
-    for (int off = lane * 12; off < len; off += 384, wp += 96, q += 512) {
-        uint32_t a0 = __ldg(wp), a1 = __ldg(wp + 1), a2 = __ldg(wp + 2);
+    int off = lane * 12;
+    if (off >= len) return;
+    // software pipeline: the next iteration's words are requested before this one's are used
+    uint32_t n0 = 0, n1 = 0, n2 = 0, n3 = 0;
+    if (PIPE) {
+        n0 = __ldg(wp); n1 = __ldg(wp + 1); n2 = __ldg(wp + 2);
+        if (SHIFTED) n3 = __ldg(wp + 3);
+    }
+    for (; off < len; off += 384, q += 512) {
+        uint32_t a0, a1, a2, a3 = 0;
+        if (PIPE) {
+            a0 = n0; a1 = n1; a2 = n2; a3 = n3;
+            wp += 96;
+            if (off + 384 < len) {
+                n0 = __ldg(wp); n1 = __ldg(wp + 1); n2 = __ldg(wp + 2);
+                if (SHIFTED) n3 = __ldg(wp + 3);
+            }
+        } else {
+            a0 = __ldg(wp); a1 = __ldg(wp + 1); a2 = __ldg(wp + 2);
+            if (SHIFTED) a3 = __ldg(wp + 3);
+            wp += 96;
+        }
         if (SHIFTED) {
-            const uint32_t a3 = __ldg(wp + 3);
             a0 = __funnelshift_r(a0, a1, s8);
             a1 = __funnelshift_r(a1, a2, s8);
             a2 = __funnelshift_r(a2, a3, s8);
         }
         const int left = len - off;
         if (left >= 12) {
-            const uint4 v = encode12(a0, a1, a2);
+            const uint4 v = encode12_mixed<NLUT>(a0, a1, a2, lut);
             if (VEC16) {
                 *reinterpret_cast<uint4 *>(q) = v;
             } else {
@@ -288,10 +362,17 @@ __device__ __forceinline__ void encode_tile_warp(const uint8_t *src, char *dst, 
 // 11 KiB config next to a 2.4 KB cloud-init text -- spread evenly and no block-wide
 // barrier is ever needed.  header: [0] n_tiles, [1] next tile, [2] warps finished (the
 // last one re-arms [1] and [2] for the next launch over the same plan).
-__global__ void __launch_bounds__(kThreads, 8)
+template <int MIN_BLOCKS, bool PIPE, int NLUT>
+__global__ void __launch_bounds__(kThreads, MIN_BLOCKS)
 b64enc_tiles(const uint8_t *__restrict__ in, char *__restrict__ out,
              const TileDesc *__restrict__ desc, int *__restrict__ header,
              const int64_t *__restrict__ in_off, int64_t n_units) {
+    __shared__ uint16_t lut_s[NLUT > 0 ? 4096 : 1];  // NLUT < 0: diagnostic skeleton
+    const uint16_t *lut = lut_s;
+    if (NLUT > 0) {
+        fill_pair_lut(lut_s);
+        __syncthreads();
+    }
     const int lane = threadIdx.x & 31;
     const int n_warps = (int)(gridDim.x * (kThreads / 32));
     const int n_tiles = header[0];
@@ -314,11 +395,11 @@ b64enc_tiles(const uint8_t *__restrict__ in, char *__restrict__ out,
         const bool words_ok = in_pos >= 3 && in_pos + len + 4 <= in_end && (dalign & 3u) == 0;
         if (words_ok) {
             if (dalign == 0) {
-                if (sh == 0) encode_tile_warp<false, true>(src, dst, len, sh, lane);
-                else encode_tile_warp<true, true>(src, dst, len, sh, lane);
+                if (sh == 0) encode_tile_warp<false, true, PIPE, NLUT>(src, dst, len, sh, lane, lut);
+                else encode_tile_warp<true, true, PIPE, NLUT>(src, dst, len, sh, lane, lut);
             } else {
-                if (sh == 0) encode_tile_warp<false, false>(src, dst, len, sh, lane);
-                else encode_tile_warp<true, false>(src, dst, len, sh, lane);
+                if (sh == 0) encode_tile_warp<false, false, PIPE, NLUT>(src, dst, len, sh, lane, lut);
+                else encode_tile_warp<true, false, PIPE, NLUT>(src, dst, len, sh, lane, lut);
             }
         } else {
             for (int off = lane * 12; off < len; off += 384)
@@ -549,10 +630,23 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
     if (n_units <= 0) return cudaSuccess;
     ScratchLayout L = scratch_layout(n_units, total_in_bytes, kEncTileIn);
     if (scratch_bytes < L.total) return cudaErrorInvalidValue;
+    using EncKernel = void (*)(const uint8_t *, char *, const TileDesc *, int *, const int64_t *, int64_t);
+    // variant 0 is the product kernel; the rest are tuning / diagnostic builds for tools/sweep_enc.py
+    static const EncKernel kVariants[] = {b64enc_tiles<8, true, 2>, b64enc_tiles<8, true, 0>,
+                                          b64enc_tiles<8, false, 0>, b64enc_tiles<8, true, 1>,
+                                          b64enc_tiles<8, true, 3>, b64enc_tiles<6, true, 2>,
+                                          b64enc_tiles<8, true, -1>, b64enc_tiles<8, true, -2>};
+    static int variant = -1;
+    if (variant < 0) {  // tuning knob for tools/; the default is variant 0
+        const char *v = getenv("KVEDGE_ENC_VARIANT");
+        variant = v ? atoi(v) : 0;
+        if (variant < 0 || variant >= (int)(sizeof kVariants / sizeof *kVariants)) variant = 0;
+    }
+    EncKernel kern = kVariants[variant];
     cudaError_t e;
     if (g_occ_enc == 0) {
         int occ = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, b64enc_tiles, kThreads, 0);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, 0);
         if (e != cudaSuccess) return e;
         g_occ_enc = occ > 0 ? occ : 1;
     }
@@ -560,7 +654,7 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
     if (grid > L.max_tiles) grid = L.max_tiles;
     if (grid < 1) grid = 1;
     char *base = static_cast<char *>(d_scratch);
-    b64enc_tiles<<<(unsigned)grid, kThreads, 0, stream>>>(
+    kern<<<(unsigned)grid, kThreads, 0, stream>>>(
         d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
         reinterpret_cast<int *>(base), d_in_off, n_units);
     return cudaGetLastError();
