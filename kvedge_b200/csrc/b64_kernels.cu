@@ -417,6 +417,234 @@ b64enc_tiles(const uint8_t *__restrict__ in, char *__restrict__ out,
     }
 }
 
+// ----------------------------------------------------------------------------- encode, streamed
+// Warp-specialised variant of the encode kernel.  One producer warp per block walks the
+// tile table and streams whole tiles (<= 12 KiB of one unit) into a shared-memory ring with
+// one 1-D bulk async copy each (cp.async.bulk global -> shared, completion on an mbarrier);
+// eight consumer warps share every stage -- warp w takes iterations w, w+8, ... of the tile,
+// 384 input bytes each -- encode from shared memory and store 16 characters per lane
+// straight to global memory.  The producer owns all scheduling (tile counter, descriptor
+// loads, alignment), so the consumers never wait on a dependent global load, and the bytes
+// in flight per SM are set by the ring depth instead of by the number of resident warps.
+namespace stream {
+
+constexpr int kStageIn = kEncTileIn;       // one tile per stage
+constexpr int kStageStride = kStageIn + 32;  // 16 bytes of alignment slack in front, 16 behind
+constexpr int kGrabMax = 8;                // tiles taken per atomic (guided: shrinks near the end)
+
+struct StageMeta {
+    char *dst;           // where this stage's characters go
+    const uint8_t *src;  // only for byte-wise stages (see flags)
+    int len;             // input bytes in this stage; < 0: no more work
+    uint32_t sh;         // offset of the first input byte inside the stage buffer (0..15)
+    int flags;           // bit0: destination 16-byte aligned; bit1: byte-wise stage (no bulk copy)
+    int pad;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+// Spin with a deadline: a protocol bug must end in a trap (reported as a launch failure),
+// never in a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity))
+        if (clock64() - t0 > 8000000000ll) __trap();
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// Iterations cw, cw+8, ... of one stage (a tile of `len` input bytes at byte offset `sh` of
+// `buf`) by consumer warp cw.
+template <bool VEC16, int kConsumerWarps, int NLUT>
+__device__ __forceinline__ void encode_stage(const uint8_t *buf, uint32_t sh, char *dst, int len,
+                                             int cw, int lane, const uint16_t *lut) {
+    const uint32_t sh4 = sh & 3u, s8 = sh4 * 8;
+    const uint32_t *wp = reinterpret_cast<const uint32_t *>(buf + (sh & ~3u)) + cw * 96 + lane * 3;
+    char *q = dst + cw * 512 + lane * 16;
+    for (int off = cw * 384 + lane * 12; off < len;
+         off += 384 * kConsumerWarps, wp += 96 * kConsumerWarps, q += 512 * kConsumerWarps) {
+        uint32_t a0 = wp[0], a1 = wp[1], a2 = wp[2];
+        if (sh4) {
+            const uint32_t a3 = wp[3];
+            a0 = __funnelshift_r(a0, a1, s8);
+            a1 = __funnelshift_r(a1, a2, s8);
+            a2 = __funnelshift_r(a2, a3, s8);
+        }
+        const int left = len - off;
+        if (left >= 12) {
+            const uint4 v = encode12_mixed<NLUT>(a0, a1, a2, lut);
+            if (VEC16) {
+                *reinterpret_cast<uint4 *>(q) = v;
+            } else {
+                uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
+                q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
+            }
+        } else {
+            const uint32_t keep = 0xFFFFFFFFu >> (8 * (3 - ((left - 1) & 3)));
+            if (left <= 4) { a0 &= keep; a1 = 0u; a2 = 0u; }
+            else if (left <= 8) { a1 &= keep; a2 = 0u; }
+            else { a2 &= keep; }
+            const uint4 v = encode12(a0, a1, a2);
+            uint32_t w[4] = {v.x, v.y, v.z, v.w};
+            const int rem = left % 3, gi = left / 3;
+            if (rem) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g)
+                    if (g == gi)
+                        w[g] = (rem == 1) ? ((w[g] & 0x0000FFFFu) | 0x3D3D0000u)
+                                          : ((w[g] & 0x00FFFFFFu) | 0x3D000000u);
+            }
+            const int nwords = (left + 2) / 3;
+            uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+                if (g < nwords) q4[g] = w[g];
+        }
+    }
+}
+
+// header: [0] n_tiles, [1] next tile, [2] blocks finished (the last one re-arms [1], [2]).
+// Dynamic shared memory: kStages * kStageStride bytes of ring.
+template <int kStages, int kConsumerWarps, int NLUT, int MIN_BLOCKS>
+__global__ void __launch_bounds__(32 * (1 + kConsumerWarps), MIN_BLOCKS)
+b64enc_stream(const uint8_t *__restrict__ in, char *__restrict__ out,
+              const TileDesc *__restrict__ desc, int *__restrict__ header,
+              const int64_t *__restrict__ in_off, int64_t n_units) {
+    extern __shared__ __align__(128) uint8_t ring[];
+    __shared__ __align__(8) uint64_t full_bar[kStages];
+    __shared__ __align__(8) uint64_t empty_bar[kStages];
+    __shared__ StageMeta meta[kStages];
+    __shared__ uint16_t lut[NLUT > 0 ? 4096 : 1];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (NLUT > 0) fill_pair_lut(lut);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], kConsumerWarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ producer
+        const int n_tiles = header[0];
+        const int64_t in_end = in_off[n_units];
+        const int n_blocks = (int)gridDim.x;
+        uint32_t c = 0;  // stages issued so far
+        // first batch: static (block b takes tile b), later batches from the counter
+        int base = (int)blockIdx.x, count = base < n_tiles ? 1 : 0;
+        while (count > 0) {
+            // this batch's descriptors, one per lane, in flight together
+            int4 d0 = make_int4(0, 0, 0, 0), d1 = make_int4(0, 0, 0, 0);
+            if (lane < count) {
+                const int4 *dp = reinterpret_cast<const int4 *>(desc + base + lane);
+                d0 = __ldg(dp);
+                d1 = __ldg(dp + 1);
+            }
+            // the next batch (guided size), requested now and used after this one
+            int nbase = 0, ncount = 0;
+            if (lane == 0) {
+                int rem = n_tiles - (base + count);
+                int g = rem / (2 * n_blocks);
+                g = g < 1 ? 1 : (g > kGrabMax ? kGrabMax : g);
+                nbase = atomicAdd(&header[1], g) + n_blocks;
+                ncount = nbase < n_tiles ? (n_tiles - nbase < g ? n_tiles - nbase : g) : 0;
+            }
+            for (int t = 0; t < count; ++t, ++c) {
+                const int64_t in_pos = ((int64_t)(uint32_t)__shfl_sync(0xffffffffu, d0.y, t) << 32) |
+                                       (uint32_t)__shfl_sync(0xffffffffu, d0.x, t);
+                const int64_t out_pos = ((int64_t)(uint32_t)__shfl_sync(0xffffffffu, d0.w, t) << 32) |
+                                        (uint32_t)__shfl_sync(0xffffffffu, d0.z, t);
+                const int len = __shfl_sync(0xffffffffu, d1.x, t);
+                if (lane != 0) continue;
+                const uint8_t *src = in + in_pos;
+                char *dst = out + out_pos;
+                const uint32_t dalign = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
+                // the bulk copy fetches whole 16-byte lines around the tile: keep it inside the blob
+                const bool bulk_ok = in_pos >= 16 && in_pos + len + 16 <= in_end && (dalign & 3u) == 0;
+                const int s = (int)(c % kStages);
+                mbar_wait(&empty_bar[s], ((c / kStages) & 1u) ^ 1u);
+                const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
+                StageMeta m;
+                m.dst = dst;
+                m.src = src;
+                m.len = len;
+                m.sh = sh;
+                m.flags = (dalign == 0 ? 1 : 0) | (bulk_ok ? 0 : 2);
+                m.pad = 0;
+                meta[s] = m;
+                if (bulk_ok) {
+                    const uint32_t bytes = (sh + (uint32_t)len + 15u) & ~15u;
+                    mbar_arrive_expect_tx(&full_bar[s], bytes);
+                    bulk_g2s(ring + s * kStageStride, src - sh, bytes, &full_bar[s]);
+                } else {
+                    mbar_arrive(&full_bar[s]);
+                }
+            }
+            base = __shfl_sync(0xffffffffu, nbase, 0);
+            count = __shfl_sync(0xffffffffu, ncount, 0);
+        }
+        if (lane == 0) {
+            // end-of-work stage, seen by every consumer warp
+            const int s = (int)(c % kStages);
+            mbar_wait(&empty_bar[s], ((c / kStages) & 1u) ^ 1u);
+            meta[s].len = -1;
+            mbar_arrive(&full_bar[s]);
+            __threadfence();
+            if (atomicAdd(&header[2], 1) == n_blocks - 1) {
+                header[1] = 0;
+                header[2] = 0;
+                __threadfence();
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ consumers
+        const int cw = warp - 1;
+        for (uint32_t c = 0;; ++c) {
+            const int s = (int)(c % kStages);
+            mbar_wait(&full_bar[s], (c / kStages) & 1u);
+            const StageMeta m = meta[s];
+            if (m.len < 0) break;
+            if (m.flags & 2) {
+                for (int off = cw * 384 + lane * 12; off < m.len; off += 384 * kConsumerWarps)
+                    encode_bytes(m.src + off, m.dst + off / 3 * 4, (m.len - off) < 12 ? (m.len - off) : 12);
+            } else if (m.flags & 1) {
+                encode_stage<true, kConsumerWarps, NLUT>(ring + s * kStageStride, m.sh, m.dst, m.len, cw, lane, lut);
+            } else {
+                encode_stage<false, kConsumerWarps, NLUT>(ring + s * kStageStride, m.sh, m.dst, m.len, cw, lane, lut);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[s]);
+        }
+    }
+}
+
+}  // namespace stream
+
 // ----------------------------------------------------------------------------- decode
 // One alphabet character -> its 6-bit value, or a value >= 64 if it is not in the
 // alphabet.
@@ -636,14 +864,47 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
                                           b64enc_tiles<8, false, 0>, b64enc_tiles<8, true, 1>,
                                           b64enc_tiles<8, true, 3>, b64enc_tiles<6, true, 2>,
                                           b64enc_tiles<8, true, -1>, b64enc_tiles<8, true, -2>};
-    static int variant = -1;
-    if (variant < 0) {  // tuning knob for tools/; the default is variant 0
+    static int variant_latched = -1;
+    if (variant_latched < 0) {  // tuning knob for tools/; the default is variant 0
         const char *v = getenv("KVEDGE_ENC_VARIANT");
-        variant = v ? atoi(v) : 0;
-        if (variant < 0 || variant >= (int)(sizeof kVariants / sizeof *kVariants)) variant = 0;
+        variant_latched = v ? atoi(v) : 0;
+        if (variant_latched < 0) variant_latched = 0;
     }
-    EncKernel kern = kVariants[variant];
+    int variant = variant_latched;
     cudaError_t e;
+    if (variant < 100) {  // streamed (bulk-copy ring) kernels; variant 0 is the product kernel
+        struct StreamVariant { EncKernel fn; int stages, consumers; };
+        static const StreamVariant kStream[] = {
+            {stream::b64enc_stream<3, 8, 2, 4>, 3, 8},  {stream::b64enc_stream<4, 8, 2, 3>, 4, 8},
+            {stream::b64enc_stream<3, 8, 1, 4>, 3, 8},  {stream::b64enc_stream<3, 8, 3, 4>, 3, 8},
+            {stream::b64enc_stream<3, 8, 0, 4>, 3, 8},  {stream::b64enc_stream<3, 12, 2, 3>, 3, 12},
+            {stream::b64enc_stream<2, 8, 2, 5>, 2, 8},  {stream::b64enc_stream<4, 12, 2, 3>, 4, 12},
+            {stream::b64enc_stream<3, 16, 2, 2>, 3, 16}, {stream::b64enc_stream<6, 16, 2, 2>, 6, 16}};
+        static int occ_s = 0;
+        const int nv = (int)(sizeof kStream / sizeof *kStream);
+        const StreamVariant &sv = kStream[variant < nv ? variant : 0];
+        const int threads = 32 * (1 + sv.consumers);
+        const size_t dyn = (size_t)sv.stages * stream::kStageStride;
+        if (occ_s == 0) {
+            e = cudaFuncSetAttribute(sv.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+            if (e != cudaSuccess) return e;
+            int occ = 0;
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sv.fn, threads, dyn);
+            if (e != cudaSuccess) return e;
+            occ_s = occ > 0 ? occ : 1;
+        }
+        int64_t grid = (int64_t)sm_count * occ_s;
+        if (grid > L.max_tiles) grid = L.max_tiles;
+        if (grid < 1) grid = 1;
+        char *base = static_cast<char *>(d_scratch);
+        sv.fn<<<(unsigned)grid, threads, dyn, stream>>>(
+            d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
+            reinterpret_cast<int *>(base), d_in_off, n_units);
+        return cudaGetLastError();
+    }
+    variant -= 100;  // 100.. : the load/store (non-streamed) kernels kept for comparison
+    if (variant < 0 || variant >= (int)(sizeof kVariants / sizeof *kVariants)) variant = 0;
+    EncKernel kern = kVariants[variant];
     if (g_occ_enc == 0) {
         int occ = 0;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, 0);
