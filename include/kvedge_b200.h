@@ -78,6 +78,29 @@ int kv_b64enc_run_dev(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_un
                       int64_t total_in_bytes, char *d_out, void *d_scratch,
                       size_t scratch_bytes, void *stream);
 
+/* kv_b64enc_batch_dev for callers that cannot supply scratch memory.  (No counterpart in the
+ * reference: this exists for the embedding side, not for the chart.)  Some hosts of this
+ * library are not able to allocate device memory at all: a process whose HBM was claimed up
+ * front by a serving engine or a framework's caching pool, a latency-critical loop that must
+ * not call cudaMalloc/cudaFree (both may synchronise the device), or a plugin that is only
+ * ever handed input and output pointers.  For them the tile table lives in a fixed array of
+ * KV_STATIC_SCRATCH_BYTES inside the library's device image; this entry point allocates
+ * nothing, on the host or on the device.
+ *  - Limit: the batch's tile table (kv_b64_scratch_bytes(n_units, total_in_bytes): about 32
+ *    bytes per unit plus 32 bytes per 12 KiB of input) must fit in KV_STATIC_SCRATCH_BYTES;
+ *    larger batches are refused with KV_ENOMEM and a message saying so.  Every GPU that
+ *    loads the library holds the array until the process exits.
+ *  - The first call on each device looks the array's device address up (once, with that
+ *    device current); make that first call outside any stream capture.
+ *  - All calls on one GPU share the array, which keeps whatever the previous call left in
+ *    it (each call rewrites everything it reads).  Two calls whose kernels overlap on the
+ *    same GPU -- different streams, different threads -- race on it: serialise them.
+ * Same arguments and results as kv_b64enc_batch_dev otherwise; asynchronous on `stream`.  */
+#define KV_STATIC_SCRATCH_BYTES (8u << 20)
+int kv_b64enc_batch_dev_static(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
+                               int64_t total_in_bytes, char *d_out, const int64_t *d_out_off,
+                               void *stream);
+
 /* Inverse of the above: what the Kubernetes API server / KubeVirt do to
  * Secret.data.userdata before exposing it as the `userdata` file consumed at
  * deployment/helm/templates/_helper.tpl:64,73 (via aziot-edge-vm.yaml:25-28,49-51).

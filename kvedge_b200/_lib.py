@@ -11,6 +11,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libkvedge_b200.so")
 
+STATIC_SCRATCH_BYTES = 8 << 20  # KV_STATIC_SCRATCH_BYTES of include/kvedge_b200.h
 KV_OK, KV_EINVAL, KV_ENODEVICE, KV_ECUDA, KV_ENOMEM, KV_ECORRUPT, KV_ETEMPLATE = 0, -1, -2, -3, -4, -5, -6
 
 # name -> (restype, argtypes); every symbol declared in include/kvedge_b200.h
@@ -27,6 +28,8 @@ SIGNATURES = {
                                      C.c_size_t, C.c_void_p]),
     "kv_b64enc_run_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
                                     C.c_void_p, C.c_size_t, C.c_void_p]),
+    "kv_b64enc_batch_dev_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
+                                             C.c_void_p, C.c_void_p]),
     "kv_b64dec_batch_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                                       C.c_void_p]),

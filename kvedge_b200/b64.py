@@ -158,6 +158,22 @@ def b64enc_device(d_in, d_in_off, d_out, d_out_off, d_scratch, total_in_bytes: O
                                          _stream_handle(stream)))
 
 
+def b64enc_device_static(d_in, d_in_off, d_out, d_out_off, total_in_bytes: Optional[int] = None,
+                         stream=None) -> None:
+    """``b64enc_device`` without a scratch argument, for callers that cannot allocate device
+    memory (HBM fully owned by another pool, allocation-free hot loops, pointer-only plugins).
+    The tile table goes into a fixed ``_lib.STATIC_SCRATCH_BYTES`` array inside the library;
+    batches whose table would not fit raise ``KvError`` (KV_ENOMEM).  Calls on one GPU share
+    that array, so do not let two of them overlap; make the first call on a device outside
+    any stream capture.  Asynchronous on ``stream``."""
+    n = d_in_off.numel() - 1
+    if total_in_bytes is None:
+        total_in_bytes = d_in.numel()
+    check(_lib.lib().kv_b64enc_batch_dev_static(d_in.data_ptr(), d_in_off.data_ptr(), n, total_in_bytes,
+                                                d_out.data_ptr(), d_out_off.data_ptr(),
+                                                _stream_handle(stream)))
+
+
 def b64enc_plan_device(d_in_off, d_out_off, d_scratch, total_in_bytes: int, stream=None) -> None:
     """Build the tile table for a packed batch (reusable while the offsets do not change)."""
     n = d_in_off.numel() - 1
@@ -189,5 +205,5 @@ def b64dec_device(d_in, d_in_off, d_out, d_out_off, d_out_len, d_status, d_scrat
 
 
 __all__ = ["b64enc", "b64dec", "b64enc_many", "b64dec_many", "b64enc_packed", "b64dec_packed",
-           "b64enc_device", "b64dec_device", "b64enc_plan_device", "b64enc_run_device", "scratch_bytes", "encode_offsets", "decode_offsets",
+           "b64enc_device", "b64enc_device_static", "b64dec_device", "b64enc_plan_device", "b64enc_run_device", "scratch_bytes", "encode_offsets", "decode_offsets",
            "encoded_len", "CorruptInputError", "KvError"]
