@@ -477,7 +477,7 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src, uint32
 
 // Iterations cw, cw+8, ... of one stage (a tile of `len` input bytes at byte offset `sh` of
 // `buf`) by consumer warp cw.
-template <bool VEC16, int kConsumerWarps, int NLUT>
+template <bool VEC16, bool SHIFTED, int kConsumerWarps, int NLUT>
 __device__ __forceinline__ void encode_stage(const uint8_t *buf, uint32_t sh, char *dst, int len,
                                              int cw, int lane, const uint16_t *lut) {
     const uint32_t sh4 = sh & 3u, s8 = sh4 * 8;
@@ -486,7 +486,7 @@ __device__ __forceinline__ void encode_stage(const uint8_t *buf, uint32_t sh, ch
     for (int off = cw * 384 + lane * 12; off < len;
          off += 384 * kConsumerWarps, wp += 96 * kConsumerWarps, q += 512 * kConsumerWarps) {
         uint32_t a0 = wp[0], a1 = wp[1], a2 = wp[2];
-        if (sh4) {
+        if (SHIFTED) {
             const uint32_t a3 = wp[3];
             a0 = __funnelshift_r(a0, a1, s8);
             a1 = __funnelshift_r(a1, a2, s8);
@@ -633,9 +633,12 @@ b64enc_stream(const uint8_t *__restrict__ in, char *__restrict__ out,
                 for (int off = cw * 384 + lane * 12; off < m.len; off += 384 * kConsumerWarps)
                     encode_bytes(m.src + off, m.dst + off / 3 * 4, (m.len - off) < 12 ? (m.len - off) : 12);
             } else if (m.flags & 1) {
-                encode_stage<true, kConsumerWarps, NLUT>(ring + s * kStageStride, m.sh, m.dst, m.len, cw, lane, lut);
+                if (m.sh & 3u)
+                    encode_stage<true, true, kConsumerWarps, NLUT>(ring + s * kStageStride, m.sh, m.dst, m.len, cw, lane, lut);
+                else
+                    encode_stage<true, false, kConsumerWarps, NLUT>(ring + s * kStageStride, m.sh, m.dst, m.len, cw, lane, lut);
             } else {
-                encode_stage<false, kConsumerWarps, NLUT>(ring + s * kStageStride, m.sh, m.dst, m.len, cw, lane, lut);
+                encode_stage<false, true, kConsumerWarps, NLUT>(ring + s * kStageStride, m.sh, m.dst, m.len, cw, lane, lut);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[s]);
