@@ -646,6 +646,226 @@ b64enc_stream(const uint8_t *__restrict__ in, char *__restrict__ out,
     }
 }
 
+// ----------------------------------------------------------------------------- decode, streamed
+// Same producer/consumer ring for the inverse transform (what Kubernetes does to
+// Secret.data.userdata before the guest reads it, _helper.tpl:64,73).  A lane takes 16
+// characters and writes 12 bytes.  Characters are mapped two at a time through a
+// 16384-entry shared-memory table indexed by the pair's two 7-bit codes (entry = the 12
+// decoded bits, or 0xFFFF if either character is outside the alphabet), which validates and
+// decodes in one lookup.  Units that are not canonical ('=' anywhere but the very end, CR/LF,
+// foreign characters, length not a multiple of four) are only *flagged* here (status -2);
+// b64dec_slow then re-decodes them with Go's exact semantics.
+constexpr int kDecStageStride = kDecTileIn + 32;
+
+__device__ __forceinline__ void fill_dec_pair_lut(uint16_t *lut) {
+    for (int i = threadIdx.x; i < 16384; i += blockDim.x) {
+        // byte offset of an entry is (c1 << 8) | (c0 << 1), i.e. index = c1 * 128 + c0
+        const uint32_t c0 = (uint32_t)i & 127u, c1 = (uint32_t)i >> 7;
+        uint32_t v0 = 0x80u, v1 = 0x80u;
+        if (c0 - 65u < 26u) v0 = c0 - 65u;
+        if (c0 - 97u < 26u) v0 = c0 - 71u;
+        if (c0 - 48u < 10u) v0 = c0 + 4u;
+        if (c0 == 43u) v0 = 62u;
+        if (c0 == 47u) v0 = 63u;
+        if (c1 - 65u < 26u) v1 = c1 - 65u;
+        if (c1 - 97u < 26u) v1 = c1 - 71u;
+        if (c1 - 48u < 10u) v1 = c1 + 4u;
+        if (c1 == 43u) v1 = 62u;
+        if (c1 == 47u) v1 = 63u;
+        lut[i] = ((v0 | v1) & 0x80u) ? (uint16_t)0xFFFFu : (uint16_t)((v0 << 6) | v1);
+    }
+}
+
+// Four characters -> 24 decoded bits (first character in the top sextet); bit 15 of *bad is
+// raised if any character is not in the alphabet (or has bit 7 set).
+__device__ __forceinline__ uint32_t decode_word_lut(uint32_t w, const uint16_t *lut, uint32_t *bad) {
+    const char *base = reinterpret_cast<const char *>(lut);
+    const uint32_t o0 = (w & 0x7F00u) | ((w << 1) & 0xFEu);
+    const uint32_t u = w >> 16;
+    const uint32_t o1 = (u & 0x7F00u) | ((u << 1) & 0xFEu);
+    const uint32_t e0 = *reinterpret_cast<const uint16_t *>(base + o0);
+    const uint32_t e1 = *reinterpret_cast<const uint16_t *>(base + o1);
+    *bad |= e0 | e1 | ((w & 0x80808080u) ? 0x8000u : 0u);
+    return (e0 << 12) | e1;
+}
+
+template <int kStages, int kConsumerWarps, int MIN_BLOCKS>
+__global__ void __launch_bounds__(32 * (1 + kConsumerWarps), MIN_BLOCKS)
+b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
+              const TileDesc *__restrict__ desc, int *__restrict__ header,
+              const int64_t *__restrict__ in_off, int64_t n_units,
+              int64_t *__restrict__ out_len, int64_t *__restrict__ status) {
+    extern __shared__ __align__(128) uint8_t ring[];
+    __shared__ __align__(8) uint64_t full_bar[kStages];
+    __shared__ __align__(8) uint64_t empty_bar[kStages];
+    __shared__ StageMeta meta[kStages];
+    __shared__ uint16_t lut[16384];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    fill_dec_pair_lut(lut);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], kConsumerWarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ producer
+        const int n_tiles = header[0];
+        const int64_t in_end = in_off[n_units];
+        const int n_blocks = (int)gridDim.x;
+        uint32_t c = 0;
+        int base = (int)blockIdx.x, count = base < n_tiles ? 1 : 0;
+        while (count > 0) {
+            int4 d0 = make_int4(0, 0, 0, 0), d1 = make_int4(0, 0, 0, 0);
+            if (lane < count) {
+                const int4 *dp = reinterpret_cast<const int4 *>(desc + base + lane);
+                d0 = __ldg(dp);
+                d1 = __ldg(dp + 1);
+            }
+            int nbase = 0, ncount = 0;
+            if (lane == 0) {
+                int rem = n_tiles - (base + count);
+                int g = rem / (2 * n_blocks);
+                g = g < 1 ? 1 : (g > kGrabMax ? kGrabMax : g);
+                nbase = atomicAdd(&header[1], g) + n_blocks;
+                ncount = nbase < n_tiles ? (n_tiles - nbase < g ? n_tiles - nbase : g) : 0;
+            }
+            for (int t = 0; t < count; ++t) {
+                const int64_t in_pos = ((int64_t)(uint32_t)__shfl_sync(0xffffffffu, d0.y, t) << 32) |
+                                       (uint32_t)__shfl_sync(0xffffffffu, d0.x, t);
+                const int64_t out_pos = ((int64_t)(uint32_t)__shfl_sync(0xffffffffu, d0.w, t) << 32) |
+                                        (uint32_t)__shfl_sync(0xffffffffu, d0.z, t);
+                const int len = __shfl_sync(0xffffffffu, d1.x, t);
+                const int unit = __shfl_sync(0xffffffffu, d1.y, t);
+                const int tflags = __shfl_sync(0xffffffffu, d1.z, t);
+                if (lane != 0) continue;
+                if (len & 3) continue;  // unit length not a multiple of 4: flagged by the plan (-2)
+                const uint8_t *src = reinterpret_cast<const uint8_t *>(in) + in_pos;
+                uint8_t *dst = out + out_pos;
+                const bool dst4 = (reinterpret_cast<uintptr_t>(dst) & 3u) == 0;
+                const bool bulk_ok = in_pos >= 16 && in_pos + len + 16 <= in_end && dst4;
+                const int s = (int)(c % kStages);
+                mbar_wait(&empty_bar[s], ((c / kStages) & 1u) ^ 1u);
+                const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
+                StageMeta m;
+                m.dst = reinterpret_cast<char *>(dst);
+                m.src = src;
+                m.len = len;
+                m.sh = sh;
+                m.flags = (tflags & 1) | (bulk_ok ? 0 : 2);   // bit0: last tile of its unit
+                m.pad = unit;
+                meta[s] = m;
+                if (bulk_ok) {
+                    const uint32_t bytes = (sh + (uint32_t)len + 15u) & ~15u;
+                    mbar_arrive_expect_tx(&full_bar[s], bytes);
+                    bulk_g2s(ring + s * kDecStageStride, src - sh, bytes, &full_bar[s]);
+                } else {
+                    mbar_arrive(&full_bar[s]);
+                }
+                ++c;
+            }
+            c = __shfl_sync(0xffffffffu, c, 0);
+            base = __shfl_sync(0xffffffffu, nbase, 0);
+            count = __shfl_sync(0xffffffffu, ncount, 0);
+        }
+        if (lane == 0) {
+            const int s = (int)(c % kStages);
+            mbar_wait(&empty_bar[s], ((c / kStages) & 1u) ^ 1u);
+            meta[s].len = -1;
+            mbar_arrive(&full_bar[s]);
+            __threadfence();
+            if (atomicAdd(&header[2], 1) == n_blocks - 1) {
+                header[1] = 0;
+                header[2] = 0;
+                __threadfence();
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ consumers
+        const int cw = warp - 1;
+        for (uint32_t c = 0;; ++c) {
+            const int s = (int)(c % kStages);
+            mbar_wait(&full_bar[s], (c / kStages) & 1u);
+            const StageMeta m = meta[s];
+            if (m.len < 0) break;
+            const int len = m.len, unit = m.pad;
+            const bool last_tile = (m.flags & 1) != 0, bytewise = (m.flags & 2) != 0;
+            const uint8_t *buf = ring + s * kDecStageStride;
+            uint8_t *dst = reinterpret_cast<uint8_t *>(m.dst);
+            const uint32_t sh4 = m.sh & 3u, s8 = sh4 * 8;
+            uint32_t bad = 0;
+            for (int off = cw * 512 + lane * 16; off < len; off += 512 * kConsumerWarps) {
+                const int nvalid = (len - off) < 16 ? (len - off) : 16;  // a multiple of 4
+                uint32_t w[4] = {0x41414141u, 0x41414141u, 0x41414141u, 0x41414141u};
+                if (!bytewise) {
+                    const uint32_t *wp = reinterpret_cast<const uint32_t *>(buf + ((m.sh + off) & ~3u));
+                    w[0] = wp[0]; w[1] = wp[1]; w[2] = wp[2]; w[3] = wp[3];
+                    if (sh4) {
+                        const uint32_t w4 = wp[4];
+                        w[0] = __funnelshift_r(w[0], w[1], s8);
+                        w[1] = __funnelshift_r(w[1], w[2], s8);
+                        w[2] = __funnelshift_r(w[2], w[3], s8);
+                        w[3] = __funnelshift_r(w[3], w4, s8);
+                    }
+                    if (nvalid < 16) {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g)
+                            if (g * 4 >= nvalid) w[g] = 0x41414141u;
+                    }
+                } else {
+                    const uint8_t *p = m.src + off;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (i < nvalid) {
+                            const uint32_t mk = 0xFFu << (8 * (i & 3));
+                            w[i >> 2] = (w[i >> 2] & ~mk) | ((uint32_t)p[i] << (8 * (i & 3)));
+                        }
+                }
+                int npad = 0;
+                const int nq = nvalid >> 2;
+                if (last_tile && off + nvalid == len) {
+                    // '=' padding is legal only in the last quantum of the unit
+#pragma unroll
+                    for (int g = 0; g < 4; ++g)
+                        if (g == nq - 1 && (w[g] >> 24) == 0x3Du) {
+                            npad = 1;
+                            w[g] = (w[g] & 0x00FFFFFFu) | 0x41000000u;
+                            if (((w[g] >> 16) & 0xFFu) == 0x3Du) {
+                                npad = 2;
+                                w[g] = (w[g] & 0xFF00FFFFu) | 0x00410000u;
+                            }
+                        }
+                    out_len[unit] = (int64_t)(m.src - reinterpret_cast<const uint8_t *>(in) - in_off[unit] + off + nvalid) / 4 * 3 - npad;
+                }
+                const uint32_t n0 = decode_word_lut(w[0], lut, &bad), n1 = decode_word_lut(w[1], lut, &bad);
+                const uint32_t n2 = decode_word_lut(w[2], lut, &bad), n3 = decode_word_lut(w[3], lut, &bad);
+                // 4 x 24 bits (big-endian inside each group) -> 12 bytes in stream order
+                const uint32_t o0 = __byte_perm(n0, n1, 0x6012);
+                const uint32_t o1 = __byte_perm(n1, n2, 0x5601);
+                const uint32_t o2 = __byte_perm(n2, n3, 0x4560);
+                uint8_t *q = dst + off / 4 * 3;
+                const int nbytes = nq * 3 - npad;
+                if (!bytewise && nbytes == 12) {
+                    uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
+                    q4[0] = o0; q4[1] = o1; q4[2] = o2;
+                } else {
+                    const uint32_t o[3] = {o0, o1, o2};
+#pragma unroll
+                    for (int i = 0; i < 12; ++i)
+                        if (i < nbytes) q[i] = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
+                }
+            }
+            if (bad & 0x8000u) status[unit] = -2;  // benign race: every writer stores the same value
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[s]);
+        }
+    }
+}
+
 }  // namespace stream
 
 // ----------------------------------------------------------------------------- decode
@@ -945,19 +1165,52 @@ cudaError_t launch_b64dec(const char *d_in, const int64_t *d_in_off, int64_t n_u
     cudaError_t e = plan(d_in_off, d_out_off, n_units, kDecTileIn, 1, L, d_scratch, d_out_len,
                          d_status, stream);
     if (e != cudaSuccess) return e;
-    if (g_occ_dec == 0) {
-        int occ = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, b64dec_tiles, kThreads, 0);
-        if (e != cudaSuccess) return e;
-        g_occ_dec = occ > 0 ? occ : 1;
+    static int dec_variant = -1;
+    if (dec_variant < 0) {  // KVEDGE_DEC_VARIANT=100 selects the older load/store kernel (tools/)
+        const char *v = getenv("KVEDGE_DEC_VARIANT");
+        dec_variant = v ? atoi(v) : 0;
+        if (dec_variant < 0) dec_variant = 0;
     }
-    int64_t grid = (int64_t)sm_count * g_occ_dec;
-    if (grid > L.max_tiles) grid = L.max_tiles;
-    if (grid < 1) grid = 1;
     char *base = static_cast<char *>(d_scratch);
-    b64dec_tiles<<<(unsigned)grid, kThreads, 0, stream>>>(
-        d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
-        reinterpret_cast<const int *>(base), d_in_off, n_units, d_out_len, d_status);
+    if (dec_variant < 100) {
+        using DecKernel = void (*)(const char *, uint8_t *, const TileDesc *, int *, const int64_t *, int64_t,
+                                   int64_t *, int64_t *);
+        struct DecVariant { DecKernel fn; int stages, consumers; };
+        static const DecVariant kDec[] = {{stream::b64dec_stream<3, 8, 3>, 3, 8}, {stream::b64dec_stream<4, 8, 3>, 4, 8},
+                                          {stream::b64dec_stream<2, 8, 3>, 2, 8}, {stream::b64dec_stream<3, 12, 2>, 3, 12},
+                                          {stream::b64dec_stream<6, 8, 2>, 6, 8}};
+        const int nv = (int)(sizeof kDec / sizeof *kDec);
+        const DecVariant &dv = kDec[dec_variant < nv ? dec_variant : 0];
+        const int threads = 32 * (1 + dv.consumers);
+        const size_t dyn = (size_t)dv.stages * stream::kDecStageStride;
+        if (g_occ_dec == 0) {
+            e = cudaFuncSetAttribute(dv.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+            if (e != cudaSuccess) return e;
+            int occ = 0;
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dv.fn, threads, dyn);
+            if (e != cudaSuccess) return e;
+            g_occ_dec = occ > 0 ? occ : 1;
+        }
+        int64_t grid = (int64_t)sm_count * g_occ_dec;
+        if (grid > L.max_tiles) grid = L.max_tiles;
+        if (grid < 1) grid = 1;
+        dv.fn<<<(unsigned)grid, threads, dyn, stream>>>(
+            d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
+            reinterpret_cast<int *>(base), d_in_off, n_units, d_out_len, d_status);
+    } else {
+        if (g_occ_dec == 0) {
+            int occ = 0;
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, b64dec_tiles, kThreads, 0);
+            if (e != cudaSuccess) return e;
+            g_occ_dec = occ > 0 ? occ : 1;
+        }
+        int64_t grid = (int64_t)sm_count * g_occ_dec;
+        if (grid > L.max_tiles) grid = L.max_tiles;
+        if (grid < 1) grid = 1;
+        b64dec_tiles<<<(unsigned)grid, kThreads, 0, stream>>>(
+            d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
+            reinterpret_cast<const int *>(base), d_in_off, n_units, d_out_len, d_status);
+    }
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     int64_t sg = (n_units + 127) / 128;

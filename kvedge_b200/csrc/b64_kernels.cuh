@@ -10,8 +10,9 @@ namespace kvedge {
 // every tile of a unit starts on a 3-byte group and its output on a 16-byte step.
 constexpr int kEncTileIn = 12288;
 constexpr int kEncTileOut = kEncTileIn / 3 * 4;
-// Input characters per decode tile: 4 rows of 256 threads x 16 characters.
-constexpr int kDecTileIn = 16384;
+// Input characters per decode tile (one ring stage of the streamed decode kernel).
+constexpr int kDecTileIn = 8192;
+constexpr int kMinTileIn = kDecTileIn < kEncTileIn ? kDecTileIn : kEncTileIn;  // sizes the scratch
 constexpr int kThreads = 256;
 constexpr int kPlanBlock = 1024;  // units per block in the plan kernels
 

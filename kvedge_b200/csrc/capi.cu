@@ -259,8 +259,8 @@ size_t kv_b64enc_len(size_t n) { return (n + 2) / 3 * 4; }
 size_t kv_b64dec_maxlen(size_t n) { return n / 4 * 3; }
 
 size_t kv_b64_scratch_bytes(int64_t n_units, int64_t total_in_bytes) {
-    // the encode tile is the smaller one, so its table is the larger of the two
-    return kvedge::scratch_layout(n_units, total_in_bytes, kvedge::kEncTileIn).total;
+    // sized for the smaller of the two tile sizes, so one buffer serves encode and decode
+    return kvedge::scratch_layout(n_units, total_in_bytes, kvedge::kMinTileIn).total;
 }
 
 int kv_b64enc_batch_dev(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
