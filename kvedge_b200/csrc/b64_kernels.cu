@@ -802,14 +802,25 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                 const int nvalid = (len - off) < 16 ? (len - off) : 16;  // a multiple of 4
                 uint32_t w[4] = {0x41414141u, 0x41414141u, 0x41414141u, 0x41414141u};
                 if (!bytewise) {
-                    const uint32_t *wp = reinterpret_cast<const uint32_t *>(buf + ((m.sh + off) & ~3u));
-                    w[0] = wp[0]; w[1] = wp[1]; w[2] = wp[2]; w[3] = wp[3];
-                    if (sh4) {
-                        const uint32_t w4 = wp[4];
-                        w[0] = __funnelshift_r(w[0], w[1], s8);
-                        w[1] = __funnelshift_r(w[1], w[2], s8);
-                        w[2] = __funnelshift_r(w[2], w[3], s8);
-                        w[3] = __funnelshift_r(w[3], w4, s8);
+                    // 16-byte loads (a lane-per-chunk LDS.128 is bank-conflict free; four LDS.32
+                    // at a 16-byte lane stride would be 4-way conflicted), then a uniform word
+                    // select and byte funnel for stages that do not start on a 16-byte boundary
+                    const uint4 *vp = reinterpret_cast<const uint4 *>(buf + off);
+                    const uint4 A = vp[0];
+                    w[0] = A.x; w[1] = A.y; w[2] = A.z; w[3] = A.w;
+                    if (m.sh) {
+                        const uint4 B = vp[1];
+                        uint32_t w4 = B.x;
+                        const uint32_t ws = m.sh >> 2;
+                        if (ws == 1) { w[0] = A.y; w[1] = A.z; w[2] = A.w; w[3] = B.x; w4 = B.y; }
+                        else if (ws == 2) { w[0] = A.z; w[1] = A.w; w[2] = B.x; w[3] = B.y; w4 = B.z; }
+                        else if (ws == 3) { w[0] = A.w; w[1] = B.x; w[2] = B.y; w[3] = B.z; w4 = B.w; }
+                        if (sh4) {
+                            w[0] = __funnelshift_r(w[0], w[1], s8);
+                            w[1] = __funnelshift_r(w[1], w[2], s8);
+                            w[2] = __funnelshift_r(w[2], w[3], s8);
+                            w[3] = __funnelshift_r(w[3], w4, s8);
+                        }
                     }
                     if (nvalid < 16) {
 #pragma unroll
@@ -1045,6 +1056,43 @@ __global__ void b64dec_slow(const char *__restrict__ in, const int64_t *__restri
     }
 }
 
+// ----------------------------------------------------------------------------- host-side plan
+// The same tile table as plan_count + plan_emit, built on the host.  The host-buffer entry
+// points know every offset already, so they write the table into pinned memory and ship it
+// with the offsets in one copy instead of launching two planning kernels per chunk.
+int64_t plan_tiles_host(const int64_t *in_off, const int64_t *out_off, int64_t n_units, int tile_in,
+                        int mode, const ScratchLayout &L, void *scratch_host, int64_t *out_len,
+                        int64_t *status) {
+    char *base = static_cast<char *>(scratch_host);
+    int *header = reinterpret_cast<int *>(base);
+    TileDesc *desc = reinterpret_cast<TileDesc *>(base + L.desc_off);
+    int64_t t = 0;
+    for (int64_t u = 0; u < n_units; ++u) {
+        const int64_t ibeg = in_off[u];
+        int64_t len = in_off[u + 1] - ibeg;
+        if (len < 0) len = 0;
+        if (mode == 1) {
+            out_len[u] = len / 4 * 3;
+            status[u] = (len & 3) ? -2 : -1;
+        }
+        for (int64_t s = 0; s < len; s += tile_in, ++t) {
+            TileDesc d;
+            d.in_pos = ibeg + s;
+            d.out_pos = out_off[u] + (mode == 0 ? s / 3 * 4 : s / 4 * 3);
+            const int64_t rem = len - s;
+            d.len = (int32_t)(rem < tile_in ? rem : tile_in);
+            d.unit = (int32_t)u;
+            d.flags = (s + tile_in >= len) ? 1 : 0;
+            d.pad = 0;
+            desc[t] = d;
+        }
+    }
+    header[0] = (int)t;
+    header[1] = 0;
+    header[2] = 0;
+    return t;
+}
+
 // ----------------------------------------------------------------------------- launchers
 static int g_occ_enc = 0, g_occ_dec = 0;
 
@@ -1103,20 +1151,27 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
             {stream::b64enc_stream<3, 8, 0, 4>, 3, 8},  {stream::b64enc_stream<3, 12, 2, 3>, 3, 12},
             {stream::b64enc_stream<2, 8, 2, 5>, 2, 8},  {stream::b64enc_stream<4, 12, 2, 3>, 4, 12},
             {stream::b64enc_stream<3, 16, 2, 2>, 3, 16}, {stream::b64enc_stream<6, 16, 2, 2>, 6, 16}};
-        static int occ_s = 0;
+        static int occ_v[16];
         const int nv = (int)(sizeof kStream / sizeof *kStream);
-        const StreamVariant &sv = kStream[variant < nv ? variant : 0];
+        // tiny batches (a single render): the all-arithmetic build, which has no table to fill
+        const bool tiny = variant == 0 && L.max_tiles <= 32;
+        const StreamVariant &sv = kStream[tiny ? 4 : (variant < nv ? variant : 0)];
         const int threads = 32 * (1 + sv.consumers);
         const size_t dyn = (size_t)sv.stages * stream::kStageStride;
-        if (occ_s == 0) {
+        static bool attr_set[16];
+        const int vi = (int)(&sv - kStream);
+        if (!attr_set[vi]) {
             e = cudaFuncSetAttribute(sv.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
             if (e != cudaSuccess) return e;
+            attr_set[vi] = true;
+        }
+        if (occ_v[vi] == 0) {
             int occ = 0;
             e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sv.fn, threads, dyn);
             if (e != cudaSuccess) return e;
-            occ_s = occ > 0 ? occ : 1;
+            occ_v[vi] = occ > 0 ? occ : 1;
         }
-        int64_t grid = (int64_t)sm_count * occ_s;
+        int64_t grid = (int64_t)sm_count * occ_v[vi];
         if (grid > L.max_tiles) grid = L.max_tiles;
         if (grid < 1) grid = 1;
         char *base = static_cast<char *>(d_scratch);
@@ -1165,6 +1220,20 @@ cudaError_t launch_b64dec(const char *d_in, const int64_t *d_in_off, int64_t n_u
     cudaError_t e = plan(d_in_off, d_out_off, n_units, kDecTileIn, 1, L, d_scratch, d_out_len,
                          d_status, stream);
     if (e != cudaSuccess) return e;
+    return launch_b64dec_run(d_in, d_in_off, n_units, total_in_bytes, d_out, d_out_off, d_out_len,
+                             d_status, d_scratch, scratch_bytes, stream, sm_count);
+}
+
+// Decode kernels over a tile table that is already in d_scratch (built by the plan kernels
+// or by plan_tiles_host); d_out_len / d_status must already hold their initial values.
+cudaError_t launch_b64dec_run(const char *d_in, const int64_t *d_in_off, int64_t n_units,
+                              int64_t total_in_bytes, uint8_t *d_out, const int64_t *d_out_off,
+                              int64_t *d_out_len, int64_t *d_status, void *d_scratch,
+                              size_t scratch_bytes, cudaStream_t stream, int sm_count) {
+    if (n_units <= 0) return cudaSuccess;
+    ScratchLayout L = scratch_layout(n_units, total_in_bytes, kDecTileIn);
+    if (scratch_bytes < L.total) return cudaErrorInvalidValue;
+    cudaError_t e;
     static int dec_variant = -1;
     if (dec_variant < 0) {  // KVEDGE_DEC_VARIANT=100 selects the older load/store kernel (tools/)
         const char *v = getenv("KVEDGE_DEC_VARIANT");

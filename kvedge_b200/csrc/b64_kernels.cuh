@@ -57,4 +57,16 @@ cudaError_t launch_b64dec(const char *d_in, const int64_t *d_in_off, int64_t n_u
                           int64_t *d_out_len, int64_t *d_status, void *d_scratch,
                           size_t scratch_bytes, cudaStream_t stream, int sm_count);
 
+cudaError_t launch_b64dec_run(const char *d_in, const int64_t *d_in_off, int64_t n_units,
+                              int64_t total_in_bytes, uint8_t *d_out, const int64_t *d_out_off,
+                              int64_t *d_out_len, int64_t *d_status, void *d_scratch,
+                              size_t scratch_bytes, cudaStream_t stream, int sm_count);
+
+// Host-side twin of the plan kernels: writes header + TileDesc table into `scratch_host`
+// (a host mirror of the scratch, laid out by L) and, for decode (mode 1), the initial
+// out_len / status values.  Returns the number of tiles.
+int64_t plan_tiles_host(const int64_t *in_off, const int64_t *out_off, int64_t n_units, int tile_in,
+                        int mode, const ScratchLayout &L, void *scratch_host, int64_t *out_len,
+                        int64_t *status);
+
 }  // namespace kvedge

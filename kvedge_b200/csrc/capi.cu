@@ -73,11 +73,12 @@ struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
     bool busy = false;
-    char *d_in = nullptr;      size_t cap_in = 0;
-    char *d_out = nullptr;     size_t cap_out = 0;
-    int64_t *d_off = nullptr;  size_t cap_off = 0;   // in_off | out_off | out_len | status
-    char *d_scratch = nullptr; size_t cap_scratch = 0;
-    int64_t *h_off = nullptr;  size_t cap_hoff = 0;  // pinned mirror of d_off
+    char *d_in = nullptr;   size_t cap_in = 0;
+    char *d_out = nullptr;  size_t cap_out = 0;
+    // control block, same layout on both sides so that ONE copy ships it:
+    //   in_off[n+1] | out_off[n+1] | out_len[n] | status[n] | pad to 256 | scratch (header, tile table)
+    char *d_ctl = nullptr;  size_t cap_ctl = 0;
+    char *h_ctl = nullptr;  size_t cap_hctl = 0;  // pinned
 };
 
 struct HostCtx {
@@ -87,8 +88,7 @@ struct HostCtx {
 };
 HostCtx g_ctx;
 
-template <typename T>
-int grow(T **p, size_t *cap, size_t need) {
+int grow(char **p, size_t *cap, size_t need) {
     if (need <= *cap) return KV_OK;
     if (*p) KV_CUDA(cudaFree(*p));
     *p = nullptr;
@@ -98,12 +98,12 @@ int grow(T **p, size_t *cap, size_t need) {
     void *q = nullptr;
     cudaError_t e = cudaMalloc(&q, want);
     if (e != cudaSuccess) return fail(KV_ENOMEM, "cudaMalloc(%zu): %s", want, cudaGetErrorString(e));
-    *p = static_cast<T *>(q);
+    *p = static_cast<char *>(q);
     *cap = want;
     return KV_OK;
 }
 
-int grow_pinned(int64_t **p, size_t *cap, size_t need) {
+int grow_pinned(char **p, size_t *cap, size_t need) {
     if (need <= *cap) return KV_OK;
     if (*p) KV_CUDA(cudaFreeHost(*p));
     *p = nullptr;
@@ -113,7 +113,7 @@ int grow_pinned(int64_t **p, size_t *cap, size_t need) {
     void *q = nullptr;
     cudaError_t e = cudaMallocHost(&q, want);
     if (e != cudaSuccess) return fail(KV_ENOMEM, "cudaMallocHost(%zu): %s", want, cudaGetErrorString(e));
-    *p = static_cast<int64_t *>(q);
+    *p = static_cast<char *>(q);
     *cap = want;
     return KV_OK;
 }
@@ -142,6 +142,9 @@ int slot_wait(Slot &s) {
 }
 
 // Run units [lo, hi) of a host packed batch through one slot. mode 0 = encode, 1 = decode.
+// The tile table is built here on the host (every offset is known) and travels with the
+// offsets in a single copy: per chunk the GPU sees one control copy, one data copy, the
+// encode (or decode) kernel and one copy back.
 int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *out,
               const int64_t *out_off, int64_t lo, int64_t hi, int64_t *out_len,
               int64_t *status, int sm_count) {
@@ -154,32 +157,44 @@ int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *ou
     // keep each unit's alignment (mod 16) identical on the device and on the host side
     const int64_t ishift = ibeg & 15, oshift = obeg & 15;
     const int tile = mode == 0 ? kvedge::kEncTileIn : kvedge::kDecTileIn;
-    kvedge::ScratchLayout L = kvedge::scratch_layout(n, in_bytes + ishift, tile);
+    const kvedge::ScratchLayout L = kvedge::scratch_layout(n, in_bytes + ishift, tile);
+    const size_t off_in = 0, off_out = (size_t)(n + 1) * 8, off_len = off_out + (size_t)(n + 1) * 8;
+    const size_t off_status = off_len + (size_t)n * 8;
+    const size_t off_scratch = (off_status + (size_t)n * 8 + 255) / 256 * 256;
+    const size_t ctl_total = off_scratch + L.total;
     if ((rc = grow(&s.d_in, &s.cap_in, (size_t)(in_bytes + ishift + 32)))) return rc;
     if ((rc = grow(&s.d_out, &s.cap_out, (size_t)(out_bytes + oshift + 32)))) return rc;
-    const size_t off_words = (size_t)(n + 1) * 2 + (mode ? (size_t)n * 2 : 0);
-    if ((rc = grow(&s.d_off, &s.cap_off, off_words * 8))) return rc;
-    if ((rc = grow_pinned(&s.h_off, &s.cap_hoff, off_words * 8))) return rc;
-    if ((rc = grow(&s.d_scratch, &s.cap_scratch, L.total))) return rc;
-    int64_t *h_in_off = s.h_off, *h_out_off = s.h_off + (n + 1);
+    if ((rc = grow(&s.d_ctl, &s.cap_ctl, ctl_total))) return rc;
+    if ((rc = grow_pinned(&s.h_ctl, &s.cap_hctl, ctl_total))) return rc;
+    int64_t *h_in_off = reinterpret_cast<int64_t *>(s.h_ctl + off_in);
+    int64_t *h_out_off = reinterpret_cast<int64_t *>(s.h_ctl + off_out);
+    int64_t *h_len = reinterpret_cast<int64_t *>(s.h_ctl + off_len);
+    int64_t *h_status = reinterpret_cast<int64_t *>(s.h_ctl + off_status);
     for (int64_t k = 0; k <= n; ++k) {
         h_in_off[k] = in_off[lo + k] - ibeg + ishift;
         h_out_off[k] = out_off[lo + k] - obeg + oshift;
     }
-    int64_t *d_in_off = s.d_off, *d_out_off = s.d_off + (n + 1);
-    int64_t *d_len = s.d_off + 2 * (n + 1), *d_status = d_len + n;
-    KV_CUDA(cudaMemcpyAsync(s.d_off, s.h_off, (size_t)(n + 1) * 16, cudaMemcpyHostToDevice, s.stream));
+    const int64_t n_tiles = kvedge::plan_tiles_host(h_in_off, h_out_off, n, tile, mode, L,
+                                                    s.h_ctl + off_scratch, h_len, h_status);
+    const size_t ctl_used = off_scratch + L.desc_off + (size_t)n_tiles * sizeof(kvedge::TileDesc);
+    KV_CUDA(cudaMemcpyAsync(s.d_ctl, s.h_ctl, ctl_used, cudaMemcpyHostToDevice, s.stream));
     if (in_bytes > 0)
         KV_CUDA(cudaMemcpyAsync(s.d_in + ishift, in + ibeg, (size_t)in_bytes, cudaMemcpyHostToDevice, s.stream));
-    cudaError_t e;
-    if (mode == 0)
-        e = kvedge::launch_b64enc(reinterpret_cast<const uint8_t *>(s.d_in), d_in_off, n,
-                                  in_bytes + ishift, s.d_out, d_out_off, s.d_scratch,
-                                  s.cap_scratch, s.stream, sm_count);
-    else
-        e = kvedge::launch_b64dec(s.d_in, d_in_off, n, in_bytes + ishift,
-                                  reinterpret_cast<uint8_t *>(s.d_out), d_out_off, d_len, d_status,
-                                  s.d_scratch, s.cap_scratch, s.stream, sm_count);
+    const int64_t *d_in_off = reinterpret_cast<const int64_t *>(s.d_ctl + off_in);
+    const int64_t *d_out_off = reinterpret_cast<const int64_t *>(s.d_ctl + off_out);
+    int64_t *d_len = reinterpret_cast<int64_t *>(s.d_ctl + off_len);
+    int64_t *d_status = reinterpret_cast<int64_t *>(s.d_ctl + off_status);
+    cudaError_t e = cudaSuccess;
+    if (n_tiles > 0) {
+        if (mode == 0)
+            e = kvedge::launch_b64enc_run(reinterpret_cast<const uint8_t *>(s.d_in), d_in_off, n,
+                                          in_bytes + ishift, s.d_out, s.d_ctl + off_scratch, L.total,
+                                          s.stream, sm_count);
+        else
+            e = kvedge::launch_b64dec_run(s.d_in, d_in_off, n, in_bytes + ishift,
+                                          reinterpret_cast<uint8_t *>(s.d_out), d_out_off, d_len, d_status,
+                                          s.d_ctl + off_scratch, L.total, s.stream, sm_count);
+    }
     if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
     if (out_bytes > 0)
         KV_CUDA(cudaMemcpyAsync(out + obeg, s.d_out + oshift, (size_t)out_bytes, cudaMemcpyDeviceToHost, s.stream));
@@ -388,9 +403,8 @@ void kv_shutdown(void) {
         if (s.busy) cudaEventSynchronize(s.done);
         if (s.d_in) cudaFree(s.d_in);
         if (s.d_out) cudaFree(s.d_out);
-        if (s.d_off) cudaFree(s.d_off);
-        if (s.d_scratch) cudaFree(s.d_scratch);
-        if (s.h_off) cudaFreeHost(s.h_off);
+        if (s.d_ctl) cudaFree(s.d_ctl);
+        if (s.h_ctl) cudaFreeHost(s.h_ctl);
         if (s.done) cudaEventDestroy(s.done);
         if (s.stream) cudaStreamDestroy(s.stream);
         s = Slot();
