@@ -18,7 +18,7 @@ LIB = os.path.join(HERE, "libkvedge_b200.so")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
-    "-Xcompiler", "-fPIC,-O3,-Wall",
+    "-Xcompiler", "-fPIC,-O3,-Wall,-pthread",
     "-shared",
 ]
 

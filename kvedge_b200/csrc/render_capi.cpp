@@ -13,7 +13,10 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <atomic>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "chart.hpp"
@@ -350,16 +353,42 @@ int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *
                       const kv_overrides *overrides, char **out, int64_t *out_off) {
     if (!chart || n_releases < 0 || !out || !out_off) return fail(KV_EINVAL, "null argument");
     std::vector<std::unique_ptr<kv_release>> rel((size_t)n_releases);
-    try {
-        for (int i = 0; i < n_releases; ++i) {
-            kv_release *r = nullptr;
-            int rc = plan_release(chart, release_names ? release_names[i] : nullptr, ns,
-                                  overrides ? &overrides[i] : nullptr, true, &r);
-            if (rc) return rc;
-            rel[(size_t)i].reset(r);
-        }
-    } catch (const std::exception &e) {
-        return fail(KV_ETEMPLATE, e.what());
+    {
+        // Installs are independent: plan them on all host threads (the templates are parsed
+        // once and only read here; every release owns its values and output).
+        unsigned n_thr = std::thread::hardware_concurrency();
+        if (n_thr == 0) n_thr = 1;
+        if (n_thr > 64) n_thr = 64;
+        if ((int)n_thr > n_releases) n_thr = (unsigned)(n_releases > 0 ? n_releases : 1);
+        std::atomic<int> next{0};
+        std::atomic<int> first_rc{KV_OK};
+        std::mutex err_mu;
+        std::string err_msg;
+        auto work = [&]() {
+            for (;;) {
+                const int i = next.fetch_add(1);
+                if (i >= n_releases || first_rc.load() != KV_OK) return;
+                try {
+                    kv_release *r = nullptr;
+                    int rc = plan_release(chart, release_names ? release_names[i] : nullptr, ns,
+                                          overrides ? &overrides[i] : nullptr, true, &r);
+                    if (rc) throw kvedge::tmpl::Error(kv_last_error());
+                    rel[(size_t)i].reset(r);
+                } catch (const std::exception &e) {
+                    std::lock_guard<std::mutex> lk(err_mu);
+                    if (first_rc.load() == KV_OK) {
+                        err_msg = e.what();
+                        first_rc.store(KV_ETEMPLATE);
+                    }
+                    return;
+                }
+            }
+        };
+        std::vector<std::thread> pool;
+        for (unsigned t = 1; t < n_thr; ++t) pool.emplace_back(work);
+        work();
+        for (auto &t : pool) t.join();
+        if (first_rc.load() != KV_OK) return fail(first_rc.load(), err_msg);
     }
     // one packed batch over every pending Secret payload of the fleet
     std::vector<int64_t> in_off(1, 0), enc_off(1, 0);

@@ -28,4 +28,14 @@ out = {
     "gpu_helm_template_fixture_us": best(lambda: c.template("r", blobs={"runtimeConfig": cfg}), 100),
     "cpu_oracle_helm_template_fixture_us": best(lambda: helmref.helm_template(chart, "r"), 30),
 }
+# fleet render through the product API: n installs planned on all host threads, one GPU batch
+n = 2048
+rels = [(f"edge-{i}", {"set": [f"nameOverride=site-{i},sshKey={workload.ssh_key(i % 64).decode()}"],
+                       "blobs": {"runtimeConfig": workload.config_toml(i % 64)}}) for i in range(n)]
+c.template_fleet(rels[:64])
+t0 = time.perf_counter(); res = c.template_fleet(rels); dt = time.perf_counter() - t0
+out["fleet_template_installs"] = n
+out["fleet_template_installs_per_s"] = n / dt
+out["fleet_template_bytes_out"] = sum(len(r) for r in res)
+out["host_threads"] = os.cpu_count()
 print(json.dumps(out))
