@@ -429,7 +429,7 @@ b64enc_tiles(const uint8_t *__restrict__ in, char *__restrict__ out,
 namespace stream {
 
 constexpr int kStageIn = kEncTileIn;       // one tile per stage
-constexpr int kStageStride = kStageIn + 32;  // 16 bytes of alignment slack in front, 16 behind
+constexpr int kStageStride = (kStageIn + 32 + 15) / 16 * 16;  // 16 bytes of slack in front and behind
 constexpr int kGrabMax = 8;                // tiles taken per atomic (guided: shrinks near the end)
 
 struct StageMeta {
@@ -655,7 +655,7 @@ b64enc_stream(const uint8_t *__restrict__ in, char *__restrict__ out,
 // decodes in one lookup.  Units that are not canonical ('=' anywhere but the very end, CR/LF,
 // foreign characters, length not a multiple of four) are only *flagged* here (status -2);
 // b64dec_slow then re-decodes them with Go's exact semantics.
-constexpr int kDecStageStride = kDecTileIn + 32;
+constexpr int kDecStageStride = (kDecTileIn + 32 + 15) / 16 * 16;
 
 __device__ __forceinline__ void fill_dec_pair_lut(uint16_t *lut) {
     for (int i = threadIdx.x; i < 16384; i += blockDim.x) {
