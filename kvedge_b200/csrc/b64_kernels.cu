@@ -689,7 +689,43 @@ __device__ __forceinline__ uint32_t decode_word_lut(uint32_t w, const uint16_t *
     return (e0 << 12) | e1;
 }
 
-template <int kStages, int kConsumerWarps, int MIN_BLOCKS>
+// Alternative table: one entry per 7-bit character code, but every entry replicated across
+// all 32 shared-memory banks (row c = 32 words).  Lane l always reads word l of a row, so a
+// lookup can never bank-conflict, whatever the text looks like; the pair table above costs
+// 4-5 wavefronts per lookup on real base64 text (ncu), this one exactly 1.
+__device__ __forceinline__ void fill_dec_char_lut(uint32_t *lut) {
+    for (int i = threadIdx.x; i < 128 * 32; i += blockDim.x) {
+        const uint32_t c = (uint32_t)i >> 5;
+        uint32_t v = 0x80000000u;
+        if (c - 65u < 26u) v = c - 65u;
+        if (c - 97u < 26u) v = c - 71u;
+        if (c - 48u < 10u) v = c + 4u;
+        if (c == 43u) v = 62u;
+        if (c == 47u) v = 63u;
+        lut[i] = v;
+    }
+}
+
+// lane4 = 4 * lane.  bad_v collects the looked-up words (bit 31 = not in the alphabet), bad_w
+// the raw characters (bit 7 of any byte = not ASCII).
+__device__ __forceinline__ uint32_t decode_word_char(uint32_t w, const uint32_t *lut, uint32_t lane4,
+                                                     uint32_t *bad_v, uint32_t *bad_w) {
+    const char *base = reinterpret_cast<const char *>(lut);
+    const uint32_t o0 = ((w << 7) & 0x3F80u) | lane4;
+    const uint32_t o1 = ((w >> 1) & 0x3F80u) | lane4;
+    const uint32_t o2 = ((w >> 9) & 0x3F80u) | lane4;
+    const uint32_t o3 = ((w >> 17) & 0x3F80u) | lane4;
+    const uint32_t v0 = *reinterpret_cast<const uint32_t *>(base + o0);
+    const uint32_t v1 = *reinterpret_cast<const uint32_t *>(base + o1);
+    const uint32_t v2 = *reinterpret_cast<const uint32_t *>(base + o2);
+    const uint32_t v3 = *reinterpret_cast<const uint32_t *>(base + o3);
+    *bad_v |= v0 | v1 | v2 | v3;
+    *bad_w |= w;
+    return ((v0 * 64u + v1) * 64u + v2) * 64u + v3;
+}
+
+// LUTKIND 0: pair table (16384 x u16); 1: bank-replicated character table (128 x 32 x u32).
+template <int kStages, int kConsumerWarps, int MIN_BLOCKS, int LUTKIND>
 __global__ void __launch_bounds__(32 * (1 + kConsumerWarps), MIN_BLOCKS)
 b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
               const TileDesc *__restrict__ desc, int *__restrict__ header,
@@ -699,10 +735,13 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
     __shared__ __align__(8) uint64_t full_bar[kStages];
     __shared__ __align__(8) uint64_t empty_bar[kStages];
     __shared__ StageMeta meta[kStages];
-    __shared__ uint16_t lut[16384];
+    __shared__ __align__(128) uint32_t lut_words[LUTKIND == 0 ? 8192 : 4096];
+    __shared__ __align__(16) uint32_t obuf[kConsumerWarps][96];  // per-warp store transpose
+    uint16_t *lut = reinterpret_cast<uint16_t *>(lut_words);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    fill_dec_pair_lut(lut);
+    if (LUTKIND == 0) fill_dec_pair_lut(lut);
+    else fill_dec_char_lut(lut_words);
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&full_bar[s], 1);
@@ -797,11 +836,49 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
             const uint8_t *buf = ring + s * kDecStageStride;
             uint8_t *dst = reinterpret_cast<uint8_t *>(m.dst);
             const uint32_t sh4 = m.sh & 3u, s8 = sh4 * 8;
-            uint32_t bad = 0;
-            for (int off = cw * 512 + lane * 16; off < len; off += 512 * kConsumerWarps) {
-                const int nvalid = (len - off) < 16 ? (len - off) : 16;  // a multiple of 4
+            uint32_t bad = 0, bad_v = 0, bad_w = 0;
+            const uint32_t lane4 = (uint32_t)lane * 4u;
+            const bool dst16 = (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
+            uint32_t *ow_buf = obuf[cw];
+            for (int ow = cw * 512; ow < len; ow += 512 * kConsumerWarps) {   // warp-uniform loop
+                const int off = ow + lane * 16;
+                // Plain iteration: all 32 lanes have 16 characters and the unit does not end here,
+                // so there is no padding to look for and nothing partial to store.
+                if (LUTKIND == 1 && !bytewise && dst16 && (ow + 512 < len || (ow + 512 == len && !last_tile))) {
+                    const uint4 *vp = reinterpret_cast<const uint4 *>(buf + off);
+                    const uint4 A = vp[0];
+                    uint32_t w0 = A.x, w1 = A.y, w2 = A.z, w3 = A.w;
+                    if (m.sh) {
+                        const uint4 B = vp[1];
+                        uint32_t w4 = B.x;
+                        const uint32_t ws = m.sh >> 2;
+                        if (ws == 1) { w0 = A.y; w1 = A.z; w2 = A.w; w3 = B.x; w4 = B.y; }
+                        else if (ws == 2) { w0 = A.z; w1 = A.w; w2 = B.x; w3 = B.y; w4 = B.z; }
+                        else if (ws == 3) { w0 = A.w; w1 = B.x; w2 = B.y; w3 = B.z; w4 = B.w; }
+                        if (sh4) {
+                            w0 = __funnelshift_r(w0, w1, s8);
+                            w1 = __funnelshift_r(w1, w2, s8);
+                            w2 = __funnelshift_r(w2, w3, s8);
+                            w3 = __funnelshift_r(w3, w4, s8);
+                        }
+                    }
+                    const uint32_t n0 = decode_word_char(w0, lut_words, lane4, &bad_v, &bad_w);
+                    const uint32_t n1 = decode_word_char(w1, lut_words, lane4, &bad_v, &bad_w);
+                    const uint32_t n2 = decode_word_char(w2, lut_words, lane4, &bad_v, &bad_w);
+                    const uint32_t n3 = decode_word_char(w3, lut_words, lane4, &bad_v, &bad_w);
+                    ow_buf[lane * 3 + 0] = __byte_perm(n0, n1, 0x6012);
+                    ow_buf[lane * 3 + 1] = __byte_perm(n1, n2, 0x5601);
+                    ow_buf[lane * 3 + 2] = __byte_perm(n2, n3, 0x4560);
+                    __syncwarp();
+                    if (lane < 24)
+                        reinterpret_cast<uint4 *>(dst + ow / 4 * 3)[lane] = reinterpret_cast<const uint4 *>(ow_buf)[lane];
+                    __syncwarp();
+                    continue;
+                }
+                const bool active = off < len;
+                const int nvalid = !active ? 0 : ((len - off) < 16 ? (len - off) : 16);  // a multiple of 4
                 uint32_t w[4] = {0x41414141u, 0x41414141u, 0x41414141u, 0x41414141u};
-                if (!bytewise) {
+                if (!bytewise && active) {
                     // 16-byte loads (a lane-per-chunk LDS.128 is bank-conflict free; four LDS.32
                     // at a 16-byte lane stride would be 4-way conflicted), then a uniform word
                     // select and byte funnel for stages that do not start on a 16-byte boundary
@@ -827,7 +904,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                         for (int g = 0; g < 4; ++g)
                             if (g * 4 >= nvalid) w[g] = 0x41414141u;
                     }
-                } else {
+                } else if (active) {
                     const uint8_t *p = m.src + off;
 #pragma unroll
                     for (int i = 0; i < 16; ++i)
@@ -838,7 +915,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                 }
                 int npad = 0;
                 const int nq = nvalid >> 2;
-                if (last_tile && off + nvalid == len) {
+                if (active && last_tile && off + nvalid == len) {
                     // '=' padding is legal only in the last quantum of the unit
 #pragma unroll
                     for (int g = 0; g < 4; ++g)
@@ -852,24 +929,44 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                         }
                     out_len[unit] = (int64_t)(m.src - reinterpret_cast<const uint8_t *>(in) - in_off[unit] + off + nvalid) / 4 * 3 - npad;
                 }
-                const uint32_t n0 = decode_word_lut(w[0], lut, &bad), n1 = decode_word_lut(w[1], lut, &bad);
-                const uint32_t n2 = decode_word_lut(w[2], lut, &bad), n3 = decode_word_lut(w[3], lut, &bad);
+                uint32_t n0, n1, n2, n3;
+                if (LUTKIND == 0) {
+                    n0 = decode_word_lut(w[0], lut, &bad); n1 = decode_word_lut(w[1], lut, &bad);
+                    n2 = decode_word_lut(w[2], lut, &bad); n3 = decode_word_lut(w[3], lut, &bad);
+                } else {
+                    n0 = decode_word_char(w[0], lut_words, lane4, &bad_v, &bad_w);
+                    n1 = decode_word_char(w[1], lut_words, lane4, &bad_v, &bad_w);
+                    n2 = decode_word_char(w[2], lut_words, lane4, &bad_v, &bad_w);
+                    n3 = decode_word_char(w[3], lut_words, lane4, &bad_v, &bad_w);
+                }
                 // 4 x 24 bits (big-endian inside each group) -> 12 bytes in stream order
                 const uint32_t o0 = __byte_perm(n0, n1, 0x6012);
                 const uint32_t o1 = __byte_perm(n1, n2, 0x5601);
                 const uint32_t o2 = __byte_perm(n2, n3, 0x4560);
                 uint8_t *q = dst + off / 4 * 3;
                 const int nbytes = nq * 3 - npad;
-                if (!bytewise && nbytes == 12) {
+                // A full warp-iteration (32 lanes x 12 bytes = 384 contiguous bytes) is transposed
+                // through shared memory so that 24 lanes can store 16 bytes each: 12 whole sectors
+                // instead of 36 byte-masked ones.
+                if (dst16 && __all_sync(0xffffffffu, !bytewise && nbytes == 12)) {
+                    ow_buf[lane * 3 + 0] = o0;
+                    ow_buf[lane * 3 + 1] = o1;
+                    ow_buf[lane * 3 + 2] = o2;
+                    __syncwarp();
+                    if (lane < 24)
+                        reinterpret_cast<uint4 *>(dst + ow / 4 * 3)[lane] = reinterpret_cast<const uint4 *>(ow_buf)[lane];
+                    __syncwarp();
+                } else if (!bytewise && nbytes == 12) {
                     uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
                     q4[0] = o0; q4[1] = o1; q4[2] = o2;
-                } else {
+                } else if (active) {
                     const uint32_t o[3] = {o0, o1, o2};
 #pragma unroll
                     for (int i = 0; i < 12; ++i)
                         if (i < nbytes) q[i] = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
                 }
             }
+            if (LUTKIND != 0) bad = ((bad_v & 0x80000000u) || (bad_w & 0x80808080u)) ? 0x8000u : 0u;
             if (bad & 0x8000u) status[unit] = -2;  // benign race: every writer stores the same value
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[s]);
@@ -1245,9 +1342,9 @@ cudaError_t launch_b64dec_run(const char *d_in, const int64_t *d_in_off, int64_t
         using DecKernel = void (*)(const char *, uint8_t *, const TileDesc *, int *, const int64_t *, int64_t,
                                    int64_t *, int64_t *);
         struct DecVariant { DecKernel fn; int stages, consumers; };
-        static const DecVariant kDec[] = {{stream::b64dec_stream<3, 8, 3>, 3, 8}, {stream::b64dec_stream<4, 8, 3>, 4, 8},
-                                          {stream::b64dec_stream<2, 8, 3>, 2, 8}, {stream::b64dec_stream<3, 12, 2>, 3, 12},
-                                          {stream::b64dec_stream<6, 8, 2>, 6, 8}};
+        static const DecVariant kDec[] = {{stream::b64dec_stream<3, 8, 4, 1>, 3, 8}, {stream::b64dec_stream<3, 8, 3, 0>, 3, 8},
+                                          {stream::b64dec_stream<4, 8, 4, 1>, 4, 8}, {stream::b64dec_stream<2, 8, 5, 1>, 2, 8},
+                                          {stream::b64dec_stream<3, 12, 3, 1>, 3, 12}};
         const int nv = (int)(sizeof kDec / sizeof *kDec);
         const DecVariant &dv = kDec[dec_variant < nv ? dec_variant : 0];
         const int threads = 32 * (1 + dv.consumers);
