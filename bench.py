@@ -293,6 +293,42 @@ def main():
     torch.cuda.synchronize()
     ms_kernel = kev0.elapsed_time(kev1) / args.steps
 
+    # ---- the inverse (what Kubernetes does to Secret.data), reported beside
+    # the headline, not part of it: decode the fleet's densely packed encodings, check identity
+    dense_off = b64.encode_offsets(in_off, align=1)
+    d_dense_off = torch.from_numpy(dense_off).cuda()
+    d_dense = torch.zeros(int(dense_off[-1]), dtype=torch.uint8, device="cuda")
+    b64.b64enc_device(d_in, d_in_off, d_dense, d_dense_off, scratch, total_in_bytes=total_in, stream=stream)
+    dec_off = b64.decode_offsets(dense_off, align=16)
+    d_dec_off = torch.from_numpy(dec_off).cuda()
+    d_dec = torch.zeros(int(dec_off[-1]) + 16, dtype=torch.uint8, device="cuda")
+    d_dlen = torch.zeros(n_units, dtype=torch.int64, device="cuda")
+    d_dst = torch.zeros(n_units, dtype=torch.int64, device="cuda")
+    dscratch = torch.empty(b64.scratch_bytes(n_units, int(dense_off[-1])), dtype=torch.uint8, device="cuda")
+
+    def dec_step():
+        b64.b64dec_device(d_dense, d_dense_off, d_dec, d_dec_off, d_dlen, d_dst, dscratch,
+                          total_in_bytes=int(dense_off[-1]), stream=stream)
+
+    for _ in range(3):
+        dec_step()
+    dev0, dev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    dev0.record(stream)
+    for _ in range(args.steps):
+        dec_step()
+    dev1.record(stream)
+    torch.cuda.synchronize()
+    ms_dec = dev0.elapsed_time(dev1) / args.steps
+    lens_t = torch.from_numpy(np.diff(in_off)).cuda()
+    if not (bool((d_dst == -1).all()) and bool((d_dlen == lens_t).all())):
+        raise SystemExit("decode round trip failed (status / length)")
+    for i in (0, 1, n_units // 2, n_units - 1):
+        a = int(dec_off[i])
+        if not torch.equal(d_dec[a:a + int(lens_t[i])], d_in[int(in_off[i]):int(in_off[i + 1])]):
+            raise SystemExit(f"decode round trip failed at unit {i}")
+    del d_dense, d_dec, dscratch
+
     t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
     if distributed:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -373,6 +409,10 @@ def main():
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": algo, "kernel_ms": ms_kernel,
                      "kernel_share_of_step": ms_kernel / ms_step},
+        "decode": {"ms_per_step": ms_dec, "GBps": (int(dense_off[-1]) + total_in) / (ms_dec * 1e-3) / 1e9,
+                   "frac_of_peak": (int(dense_off[-1]) + total_in) / (ms_dec * 1e-3) / 1e9 / peak,
+                   "round_trip_identity": True,
+                   "what": "kv_b64dec_batch_dev over the fleet's encodings (plan + b64dec_stream + b64dec_slow)"},
         "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": f"{cpu_units // 2} installs x {cpu_passes} passes in {cpu_dt:.1f} s, "
                                    f"oracle/b64_ref.c over {threads} host threads",
