@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -66,8 +67,17 @@ int sm_count_of_current_device(int *out) {
 }
 
 // ------------------------------------------------------------------ host-buffer pipeline
-constexpr int kSlots = 3;
-constexpr int64_t kChunkBytes = 32ll << 20;  // input bytes per pipeline chunk
+constexpr int kSlots = 4;
+constexpr int64_t kChunkBytesDefault = 32ll << 20;  // input bytes per pipeline chunk
+
+int64_t chunk_bytes() {
+    static int64_t v = 0;
+    if (v == 0) {  // KVEDGE_CHUNK_MB: tuning knob for tools/
+        const char *e = getenv("KVEDGE_CHUNK_MB");
+        v = e && atoi(e) > 0 ? (int64_t)atoi(e) << 20 : kChunkBytesDefault;
+    }
+    return v;
+}
 
 struct Slot {
     cudaStream_t stream = nullptr;
@@ -233,7 +243,7 @@ int run_host_batch(int mode, const char *in, const int64_t *in_off, int64_t n_un
     int turn = 0;
     while (lo < n_units) {
         int64_t hi = lo + 1;
-        while (hi < n_units && in_off[hi + 1] - in_off[lo] <= kChunkBytes) ++hi;
+        while (hi < n_units && in_off[hi + 1] - in_off[lo] <= chunk_bytes()) ++hi;
         rc = run_chunk(g_ctx.slot[turn % kSlots], mode, in, in_off, out, out_off, lo, hi, out_len,
                        status, sms);
         if (rc) break;
