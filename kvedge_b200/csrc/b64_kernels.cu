@@ -211,6 +211,22 @@ __device__ __forceinline__ void fill_pair_lut(uint16_t *lut) {
 
 // 12 input bytes in three little-endian words -> 16 output characters.  NLUT of the four
 // groups go through the pair table, the others through the arithmetic mapping.
+// Four 3-byte groups (each as b0<<24 | b1<<16 | b2<<8 | x) -> 16 characters.
+template <int NLUT>
+__device__ __forceinline__ uint4 encode_groups(uint32_t g0, uint32_t g1, uint32_t g2, uint32_t g3,
+                                               const uint16_t *lut) {
+    uint4 r;
+    if (NLUT < 0) {  // diagnostic skeleton: memory traffic only, wrong bytes
+        r.x = g0; r.y = g1; r.z = g2; r.w = g0 ^ g3;
+        return r;
+    }
+    r.x = encode_group(g0);
+    r.y = NLUT >= 1 ? encode_group_lut(g1, lut) : encode_group(g1);
+    r.z = NLUT >= 3 ? encode_group_lut(g2, lut) : encode_group(g2);
+    r.w = NLUT >= 2 ? encode_group_lut(g3, lut) : encode_group(g3);
+    return r;
+}
+
 template <int NLUT>
 __device__ __forceinline__ uint4 encode12_mixed(uint32_t a0, uint32_t a1, uint32_t a2, const uint16_t *lut) {
     uint4 r;
@@ -477,24 +493,34 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src, uint32
 
 // Iterations cw, cw+8, ... of one stage (a tile of `len` input bytes at byte offset `sh` of
 // `buf`) by consumer warp cw.
-template <bool VEC16, bool SHIFTED, int kConsumerWarps, int NLUT>
+template <bool VEC16, bool SHIFTED, int kConsumerWarps, int NLUT, bool SELP>
 __device__ __forceinline__ void encode_stage(const uint8_t *buf, uint32_t sh, char *dst, int len,
                                              int cw, int lane, const uint16_t *lut) {
     const uint32_t sh4 = sh & 3u, s8 = sh4 * 8;
     const uint32_t *wp = reinterpret_cast<const uint32_t *>(buf + (sh & ~3u)) + cw * 96 + lane * 3;
     char *q = dst + cw * 512 + lane * 16;
+    // A stage that does not start on a word boundary needs no shifting at all: the byte
+    // permutes that build the four 3-byte groups simply pick from one byte further along.
+    // Group g starts at byte 3g + sh4 of the lane's four words; the selectors are uniform.
+    auto sel_of = [](uint32_t o) { return (o << 12) | ((o + 1) << 8) | ((o + 2) << 4) | (o + 2); };
+    const uint32_t sel0 = sel_of(sh4), sel1 = sel_of(sh4 - 1u), sel2 = sel_of(sh4 + 2u), sel3 = sel_of(sh4 + 1u);
     for (int off = cw * 384 + lane * 12; off < len;
          off += 384 * kConsumerWarps, wp += 96 * kConsumerWarps, q += 512 * kConsumerWarps) {
-        uint32_t a0 = wp[0], a1 = wp[1], a2 = wp[2];
-        if (SHIFTED) {
-            const uint32_t a3 = wp[3];
+        uint32_t a0 = wp[0], a1 = wp[1], a2 = wp[2], a3 = 0;
+        if (SHIFTED) a3 = wp[3];
+        if (SHIFTED && !SELP) {
             a0 = __funnelshift_r(a0, a1, s8);
             a1 = __funnelshift_r(a1, a2, s8);
             a2 = __funnelshift_r(a2, a3, s8);
         }
         const int left = len - off;
         if (left >= 12) {
-            const uint4 v = encode12_mixed<NLUT>(a0, a1, a2, lut);
+            uint4 v;
+            if (SHIFTED && SELP)
+                v = encode_groups<NLUT>(__byte_perm(a0, a1, sel0), __byte_perm(a1, a2, sel1),
+                                        __byte_perm(a1, a2, sel2), __byte_perm(a2, a3, sel3), lut);
+            else
+                v = encode12_mixed<NLUT>(a0, a1, a2, lut);
             if (VEC16) {
                 *reinterpret_cast<uint4 *>(q) = v;
             } else {
@@ -502,6 +528,11 @@ __device__ __forceinline__ void encode_stage(const uint8_t *buf, uint32_t sh, ch
                 q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
             }
         } else {
+            if (SHIFTED && SELP) {
+                a0 = __funnelshift_r(a0, a1, s8);
+                a1 = __funnelshift_r(a1, a2, s8);
+                a2 = __funnelshift_r(a2, a3, s8);
+            }
             const uint32_t keep = 0xFFFFFFFFu >> (8 * (3 - ((left - 1) & 3)));
             if (left <= 4) { a0 &= keep; a1 = 0u; a2 = 0u; }
             else if (left <= 8) { a1 &= keep; a2 = 0u; }
@@ -526,8 +557,10 @@ __device__ __forceinline__ void encode_stage(const uint8_t *buf, uint32_t sh, ch
 }
 
 // header: [0] n_tiles, [1] next tile, [2] blocks finished (the last one re-arms [1], [2]).
-// Dynamic shared memory: kStages * kStageStride bytes of ring.
-template <int kStages, int kConsumerWarps, int NLUT, int MIN_BLOCKS>
+// Dynamic shared memory: the ring.  RING == 0: kStages fixed slots of kStageStride bytes.
+// RING > 0: a byte ring of RING bytes shared by kStages slots; every tile takes only the space
+// it needs (rounded to 128 bytes), so short tiles leave room for more tiles in flight.
+template <int kStages, int kConsumerWarps, int NLUT, int MIN_BLOCKS, int RING = 0, bool SELP = false>
 __global__ void __launch_bounds__(32 * (1 + kConsumerWarps), MIN_BLOCKS)
 b64enc_stream(const uint8_t *__restrict__ in, char *__restrict__ out,
               const TileDesc *__restrict__ desc, int *__restrict__ header,
@@ -536,6 +569,7 @@ b64enc_stream(const uint8_t *__restrict__ in, char *__restrict__ out,
     __shared__ __align__(8) uint64_t full_bar[kStages];
     __shared__ __align__(8) uint64_t empty_bar[kStages];
     __shared__ StageMeta meta[kStages];
+    __shared__ uint32_t ring_start[kStages];  // producer only: where each in-flight tile starts
     __shared__ uint16_t lut[NLUT > 0 ? 4096 : 1];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -555,6 +589,8 @@ b64enc_stream(const uint8_t *__restrict__ in, char *__restrict__ out,
         const int64_t in_end = in_off[n_units];
         const int n_blocks = (int)gridDim.x;
         uint32_t c = 0;  // stages issued so far
+        // byte-ring bookkeeping (RING > 0, lane 0 only): uses [waited, c) are in flight
+        uint32_t head = 0, waited = 0;
         // first batch: static (block b takes tile b), later batches from the counter
         int base = (int)blockIdx.x, count = base < n_tiles ? 1 : 0;
         while (count > 0) {
@@ -587,20 +623,46 @@ b64enc_stream(const uint8_t *__restrict__ in, char *__restrict__ out,
                 // the bulk copy fetches whole 16-byte lines around the tile: keep it inside the blob
                 const bool bulk_ok = in_pos >= 16 && in_pos + len + 16 <= in_end && (dalign & 3u) == 0;
                 const int s = (int)(c % kStages);
-                mbar_wait(&empty_bar[s], ((c / kStages) & 1u) ^ 1u);
                 const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
+                uint32_t boff = (uint32_t)s * kStageStride;
+                if (RING == 0) {
+                    mbar_wait(&empty_bar[s], ((c / kStages) & 1u) ^ 1u);
+                } else {
+                    // the slot itself: use c - kStages must be finished
+                    while (waited + kStages <= c) {
+                        mbar_wait(&empty_bar[waited % kStages], (waited / kStages) & 1u);
+                        ++waited;
+                    }
+                    // space for this tile (+16 bytes the consumers may read past the end)
+                    const uint32_t need = (sh + (uint32_t)len + 16u + 127u) & ~127u;
+                    for (;;) {
+                        if (waited == c) { head = 0; break; }              // nothing in flight
+                        const uint32_t tail = ring_start[waited % kStages];  // oldest in-flight region
+                        if (head > tail) {                                    // in flight: [tail, head)
+                            if (head + need <= (uint32_t)RING) break;
+                            if (need <= tail) { head = 0; break; }            // wrap to the front
+                        } else if (head + need <= tail) {                     // in flight: [tail, ..) + [0, head)
+                            break;
+                        }
+                        mbar_wait(&empty_bar[waited % kStages], (waited / kStages) & 1u);
+                        ++waited;
+                    }
+                    boff = head;
+                    ring_start[s] = head;
+                    head += need;
+                }
                 StageMeta m;
                 m.dst = dst;
                 m.src = src;
                 m.len = len;
                 m.sh = sh;
                 m.flags = (dalign == 0 ? 1 : 0) | (bulk_ok ? 0 : 2);
-                m.pad = 0;
+                m.pad = (int)boff;
                 meta[s] = m;
                 if (bulk_ok) {
                     const uint32_t bytes = (sh + (uint32_t)len + 15u) & ~15u;
                     mbar_arrive_expect_tx(&full_bar[s], bytes);
-                    bulk_g2s(ring + s * kStageStride, src - sh, bytes, &full_bar[s]);
+                    bulk_g2s(ring + boff, src - sh, bytes, &full_bar[s]);
                 } else {
                     mbar_arrive(&full_bar[s]);
                 }
@@ -611,7 +673,14 @@ b64enc_stream(const uint8_t *__restrict__ in, char *__restrict__ out,
         if (lane == 0) {
             // end-of-work stage, seen by every consumer warp
             const int s = (int)(c % kStages);
-            mbar_wait(&empty_bar[s], ((c / kStages) & 1u) ^ 1u);
+            if (RING == 0) {
+                mbar_wait(&empty_bar[s], ((c / kStages) & 1u) ^ 1u);
+            } else {
+                while (waited + kStages <= c) {
+                    mbar_wait(&empty_bar[waited % kStages], (waited / kStages) & 1u);
+                    ++waited;
+                }
+            }
             meta[s].len = -1;
             mbar_arrive(&full_bar[s]);
             __threadfence();
@@ -629,16 +698,20 @@ b64enc_stream(const uint8_t *__restrict__ in, char *__restrict__ out,
             mbar_wait(&full_bar[s], (c / kStages) & 1u);
             const StageMeta m = meta[s];
             if (m.len < 0) break;
+            const uint8_t *buf = ring + m.pad;
             if (m.flags & 2) {
                 for (int off = cw * 384 + lane * 12; off < m.len; off += 384 * kConsumerWarps)
                     encode_bytes(m.src + off, m.dst + off / 3 * 4, (m.len - off) < 12 ? (m.len - off) : 12);
             } else if (m.flags & 1) {
                 if (m.sh & 3u)
-                    encode_stage<true, true, kConsumerWarps, NLUT>(ring + s * kStageStride, m.sh, m.dst, m.len, cw, lane, lut);
+                    encode_stage<true, true, kConsumerWarps, NLUT, SELP>(buf, m.sh, m.dst, m.len, cw, lane, lut);
                 else
-                    encode_stage<true, false, kConsumerWarps, NLUT>(ring + s * kStageStride, m.sh, m.dst, m.len, cw, lane, lut);
+                    encode_stage<true, false, kConsumerWarps, NLUT, SELP>(buf, m.sh, m.dst, m.len, cw, lane, lut);
             } else {
-                encode_stage<false, true, kConsumerWarps, NLUT>(ring + s * kStageStride, m.sh, m.dst, m.len, cw, lane, lut);
+                if (m.sh & 3u)
+                    encode_stage<false, true, kConsumerWarps, NLUT, SELP>(buf, m.sh, m.dst, m.len, cw, lane, lut);
+                else
+                    encode_stage<false, false, kConsumerWarps, NLUT, SELP>(buf, m.sh, m.dst, m.len, cw, lane, lut);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[s]);
@@ -1241,20 +1314,23 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
     int variant = variant_latched;
     cudaError_t e;
     if (variant < 100) {  // streamed (bulk-copy ring) kernels; variant 0 is the product kernel
-        struct StreamVariant { EncKernel fn; int stages, consumers; };
+        struct StreamVariant { EncKernel fn; int stages, consumers, ring; };
         static const StreamVariant kStream[] = {
             {stream::b64enc_stream<3, 8, 2, 4>, 3, 8},  {stream::b64enc_stream<4, 8, 2, 3>, 4, 8},
             {stream::b64enc_stream<3, 8, 1, 4>, 3, 8},  {stream::b64enc_stream<3, 8, 3, 4>, 3, 8},
             {stream::b64enc_stream<3, 8, 0, 4>, 3, 8},  {stream::b64enc_stream<3, 12, 2, 3>, 3, 12},
             {stream::b64enc_stream<2, 8, 2, 5>, 2, 8},  {stream::b64enc_stream<4, 12, 2, 3>, 4, 12},
-            {stream::b64enc_stream<3, 16, 2, 2>, 3, 16}, {stream::b64enc_stream<6, 16, 2, 2>, 6, 16}};
+            {stream::b64enc_stream<3, 16, 2, 2>, 3, 16}, {stream::b64enc_stream<6, 16, 2, 2>, 6, 16},
+            {stream::b64enc_stream<8, 8, 2, 4, 36352>, 8, 8, 36352}, {stream::b64enc_stream<6, 8, 2, 4, 36352>, 6, 8, 36352},
+            {stream::b64enc_stream<12, 8, 2, 4, 36352>, 12, 8, 36352}, {stream::b64enc_stream<8, 8, 2, 3, 57344>, 8, 8, 57344},
+            {stream::b64enc_stream<3, 8, -1, 4>, 3, 8, 0}, {stream::b64enc_stream<3, 8, 2, 4, 0, true>, 3, 8, 0}};
         static int occ_v[16];
         const int nv = (int)(sizeof kStream / sizeof *kStream);
         // tiny batches (a single render): the all-arithmetic build, which has no table to fill
         const bool tiny = variant == 0 && L.max_tiles <= 32;
         const StreamVariant &sv = kStream[tiny ? 4 : (variant < nv ? variant : 0)];
         const int threads = 32 * (1 + sv.consumers);
-        const size_t dyn = (size_t)sv.stages * stream::kStageStride;
+        const size_t dyn = sv.ring ? (size_t)sv.ring : (size_t)sv.stages * stream::kStageStride;
         static bool attr_set[16];
         const int vi = (int)(&sv - kStream);
         if (!attr_set[vi]) {
