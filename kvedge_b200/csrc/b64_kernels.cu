@@ -168,11 +168,13 @@ __device__ __forceinline__ uint32_t encode_group(uint32_t np) {
         "mad.lo.u32 xb, m3, 65536, xb;\n\t"        // v3 -> lane 3
         "add.u32 p1, xb, 0x7F7F7F7F;\n\t"          // bit 7 of each lane: v > 25
         "sub.u32 p2, 0x9A9A9A9A, xb;\n\t"          //                     v <= 51
-        "sub.u32 p3, 0xA4A4A4A4, xb;\n\t"          //                     v <= 61
-        "add.u32 p4, xb, 0x5A5A5A5A;\n\t"          //                     v > 62
+        "add.u32 p4, xb, 0x5B5B5B5B;\n\t"          // x + 0x42..: bit 7 = v > 61, bit 0 = v & 1
+        "shl.b32 t, p4, 7;\n\t"
+        "not.b32 p3, p4;\n\t"
+        "and.b32 p4, p4, t;\n\t"                   // v > 61 and odd  <=>  v == 63
         "and.b32 p1, p1, 0x80808080;\n\t"
         "and.b32 p2, p2, 0x80808080;\n\t"
-        "and.b32 p3, p3, 0x80808080;\n\t"
+        "and.b32 p3, p3, 0x80808080;\n\t"          // v <= 61
         "and.b32 p4, p4, 0x80808080;\n\t"
         "mul.hi.u32 t, p1, 0x0C000000;\n\t"        // + 6 per flagged lane
         "add.u32 xb, xb, t;\n\t"
@@ -220,7 +222,7 @@ __device__ __forceinline__ uint4 encode_groups(uint32_t g0, uint32_t g1, uint32_
         r.x = g0; r.y = g1; r.z = g2; r.w = g0 ^ g3;
         return r;
     }
-    r.x = encode_group(g0);
+    r.x = NLUT >= 4 ? encode_group_lut(g0, lut) : encode_group(g0);
     r.y = NLUT >= 1 ? encode_group_lut(g1, lut) : encode_group(g1);
     r.z = NLUT >= 3 ? encode_group_lut(g2, lut) : encode_group(g2);
     r.w = NLUT >= 2 ? encode_group_lut(g3, lut) : encode_group(g3);
@@ -236,11 +238,7 @@ __device__ __forceinline__ uint4 encode12_mixed(uint32_t a0, uint32_t a1, uint32
     }
     const uint32_t g0 = __byte_perm(a0, 0u, 0x0124), g1 = __byte_perm(a0, a1, 0x3455);
     const uint32_t g2 = __byte_perm(a1, a2, 0x2344), g3 = __byte_perm(a2, 0u, 0x1233);
-    r.x = encode_group(g0);
-    r.y = NLUT >= 1 ? encode_group_lut(g1, lut) : encode_group(g1);
-    r.z = NLUT >= 3 ? encode_group_lut(g2, lut) : encode_group(g2);
-    r.w = NLUT >= 2 ? encode_group_lut(g3, lut) : encode_group(g3);
-    return r;
+    return encode_groups<NLUT>(g0, g1, g2, g3, lut);
 }
 
 __device__ __forceinline__ uint4 encode12(uint32_t a0, uint32_t a1, uint32_t a2) {
@@ -1323,7 +1321,7 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
             {stream::b64enc_stream<3, 16, 2, 2>, 3, 16}, {stream::b64enc_stream<6, 16, 2, 2>, 6, 16},
             {stream::b64enc_stream<8, 8, 2, 4, 36352>, 8, 8, 36352}, {stream::b64enc_stream<6, 8, 2, 4, 36352>, 6, 8, 36352},
             {stream::b64enc_stream<12, 8, 2, 4, 36352>, 12, 8, 36352}, {stream::b64enc_stream<8, 8, 2, 3, 57344>, 8, 8, 57344},
-            {stream::b64enc_stream<3, 8, -1, 4>, 3, 8, 0}, {stream::b64enc_stream<3, 8, 2, 4, 0, true>, 3, 8, 0}};
+            {stream::b64enc_stream<3, 8, -1, 4>, 3, 8, 0}, {stream::b64enc_stream<3, 8, 2, 4, 0, true>, 3, 8, 0}, {stream::b64enc_stream<3, 8, 4, 4>, 3, 8, 0}};
         static int occ_v[16];
         const int nv = (int)(sizeof kStream / sizeof *kStream);
         // tiny batches (a single render): the all-arithmetic build, which has no table to fill
