@@ -795,6 +795,47 @@ __device__ __forceinline__ uint32_t decode_word_char(uint32_t w, const uint32_t 
     return ((v0 * 64u + v1) * 64u + v2) * 64u + v3;
 }
 
+// The plain iterations of one stage for one consumer warp: warp-iterations [ow, plain_end) in
+// steps of kConsumerWarps, all 32 lanes full, no padding possible.  WS (0..3) is the word
+// offset and BSH the byte offset of the stage's first character inside its 16-byte chunk;
+// both are compile-time here so that the loop body has no selects or branches.
+template <int WS, bool BSH, int kConsumerWarps>
+__device__ __forceinline__ void decode_plain(const uint8_t *buf, const uint32_t *lut_words, uint32_t *ow_buf,
+                                             uint8_t *dst, int ow, int plain_end, uint32_t s8, int lane,
+                                             uint32_t *bad_v, uint32_t *bad_w) {
+    const uint32_t lane4 = (uint32_t)lane * 4u;
+    const uint4 *vp = reinterpret_cast<const uint4 *>(buf + ow + lane * 16);
+    uint4 *qp = reinterpret_cast<uint4 *>(dst + ow / 4 * 3) + lane;
+    const uint4 *tp = reinterpret_cast<const uint4 *>(ow_buf) + lane;
+    uint32_t *sp = ow_buf + lane * 3;
+    for (; ow < plain_end; ow += 512 * kConsumerWarps, vp += 32 * kConsumerWarps, qp += 24 * kConsumerWarps) {
+        const uint4 A = vp[0];
+        uint4 B = make_uint4(0, 0, 0, 0);
+        if (WS != 0 || BSH) B = vp[1];
+        uint32_t w0, w1, w2, w3, w4;
+        if (WS == 0) { w0 = A.x; w1 = A.y; w2 = A.z; w3 = A.w; w4 = B.x; }
+        else if (WS == 1) { w0 = A.y; w1 = A.z; w2 = A.w; w3 = B.x; w4 = B.y; }
+        else if (WS == 2) { w0 = A.z; w1 = A.w; w2 = B.x; w3 = B.y; w4 = B.z; }
+        else { w0 = A.w; w1 = B.x; w2 = B.y; w3 = B.z; w4 = B.w; }
+        if (BSH) {
+            w0 = __funnelshift_r(w0, w1, s8);
+            w1 = __funnelshift_r(w1, w2, s8);
+            w2 = __funnelshift_r(w2, w3, s8);
+            w3 = __funnelshift_r(w3, w4, s8);
+        }
+        const uint32_t n0 = decode_word_char(w0, lut_words, lane4, bad_v, bad_w);
+        const uint32_t n1 = decode_word_char(w1, lut_words, lane4, bad_v, bad_w);
+        const uint32_t n2 = decode_word_char(w2, lut_words, lane4, bad_v, bad_w);
+        const uint32_t n3 = decode_word_char(w3, lut_words, lane4, bad_v, bad_w);
+        sp[0] = __byte_perm(n0, n1, 0x6012);
+        sp[1] = __byte_perm(n1, n2, 0x5601);
+        sp[2] = __byte_perm(n2, n3, 0x4560);
+        __syncwarp();
+        if (lane < 24) *qp = *tp;
+        __syncwarp();
+    }
+}
+
 // LUTKIND 0: pair table (16384 x u16); 1: bank-replicated character table (128 x 32 x u32).
 template <int kStages, int kConsumerWarps, int MIN_BLOCKS, int LUTKIND>
 __global__ void __launch_bounds__(32 * (1 + kConsumerWarps), MIN_BLOCKS)
@@ -911,41 +952,33 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
             const uint32_t lane4 = (uint32_t)lane * 4u;
             const bool dst16 = (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
             uint32_t *ow_buf = obuf[cw];
-            for (int ow = cw * 512; ow < len; ow += 512 * kConsumerWarps) {   // warp-uniform loop
-                const int off = ow + lane * 16;
-                // Plain iteration: all 32 lanes have 16 characters and the unit does not end here,
-                // so there is no padding to look for and nothing partial to store.
-                if (LUTKIND == 1 && !bytewise && dst16 && (ow + 512 < len || (ow + 512 == len && !last_tile))) {
-                    const uint4 *vp = reinterpret_cast<const uint4 *>(buf + off);
-                    const uint4 A = vp[0];
-                    uint32_t w0 = A.x, w1 = A.y, w2 = A.z, w3 = A.w;
-                    if (m.sh) {
-                        const uint4 B = vp[1];
-                        uint32_t w4 = B.x;
-                        const uint32_t ws = m.sh >> 2;
-                        if (ws == 1) { w0 = A.y; w1 = A.z; w2 = A.w; w3 = B.x; w4 = B.y; }
-                        else if (ws == 2) { w0 = A.z; w1 = A.w; w2 = B.x; w3 = B.y; w4 = B.z; }
-                        else if (ws == 3) { w0 = A.w; w1 = B.x; w2 = B.y; w3 = B.z; w4 = B.w; }
-                        if (sh4) {
-                            w0 = __funnelshift_r(w0, w1, s8);
-                            w1 = __funnelshift_r(w1, w2, s8);
-                            w2 = __funnelshift_r(w2, w3, s8);
-                            w3 = __funnelshift_r(w3, w4, s8);
-                        }
+            // Plain iterations (all 32 lanes full, the unit cannot end inside) go through the
+            // branch-free templated loop; whatever is left -- at most the stage's last
+            // warp-iteration -- takes the general code below.
+            int ow0 = cw * 512;
+            if (LUTKIND == 1 && !bytewise && dst16) {
+                const int plain_len = last_tile ? len - 1 : len;          // iterations with ow + 512 <= plain_len
+                int n_it = plain_len >= ow0 + 512 ? (plain_len - ow0 - 512) / (512 * kConsumerWarps) + 1 : 0;
+                const int plain_end = ow0 + n_it * 512 * kConsumerWarps;  // first ow not handled here
+                if (n_it > 0) {
+                    const uint32_t ws = m.sh >> 2;
+                    const uint8_t *cb = buf + (m.sh & ~15u);               // == buf: m.sh < 16
+                    if (sh4 == 0) {
+                        if (ws == 0) decode_plain<0, false, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        else if (ws == 1) decode_plain<1, false, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        else if (ws == 2) decode_plain<2, false, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        else decode_plain<3, false, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                    } else {
+                        if (ws == 0) decode_plain<0, true, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        else if (ws == 1) decode_plain<1, true, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        else if (ws == 2) decode_plain<2, true, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        else decode_plain<3, true, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
                     }
-                    const uint32_t n0 = decode_word_char(w0, lut_words, lane4, &bad_v, &bad_w);
-                    const uint32_t n1 = decode_word_char(w1, lut_words, lane4, &bad_v, &bad_w);
-                    const uint32_t n2 = decode_word_char(w2, lut_words, lane4, &bad_v, &bad_w);
-                    const uint32_t n3 = decode_word_char(w3, lut_words, lane4, &bad_v, &bad_w);
-                    ow_buf[lane * 3 + 0] = __byte_perm(n0, n1, 0x6012);
-                    ow_buf[lane * 3 + 1] = __byte_perm(n1, n2, 0x5601);
-                    ow_buf[lane * 3 + 2] = __byte_perm(n2, n3, 0x4560);
-                    __syncwarp();
-                    if (lane < 24)
-                        reinterpret_cast<uint4 *>(dst + ow / 4 * 3)[lane] = reinterpret_cast<const uint4 *>(ow_buf)[lane];
-                    __syncwarp();
-                    continue;
+                    ow0 = plain_end;
                 }
+            }
+            for (int ow = ow0; ow < len; ow += 512 * kConsumerWarps) {   // warp-uniform loop
+                const int off = ow + lane * 16;
                 const bool active = off < len;
                 const int nvalid = !active ? 0 : ((len - off) < 16 ? (len - off) : 16);  // a multiple of 4
                 uint32_t w[4] = {0x41414141u, 0x41414141u, 0x41414141u, 0x41414141u};

@@ -11,7 +11,7 @@ namespace kvedge {
 constexpr int kEncTileIn = 12288;
 constexpr int kEncTileOut = kEncTileIn / 3 * 4;
 // Input characters per decode tile (one ring stage of the streamed decode kernel).
-constexpr int kDecTileIn = 8192;
+constexpr int kDecTileIn = 16384;
 constexpr int kMinTileIn = kDecTileIn < kEncTileIn ? kDecTileIn : kEncTileIn;  // sizes the scratch
 constexpr int kThreads = 256;
 constexpr int kPlanBlock = 1024;  // units per block in the plan kernels
