@@ -1355,19 +1355,22 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
             {stream::b64enc_stream<8, 8, 2, 4, 36352>, 8, 8, 36352}, {stream::b64enc_stream<6, 8, 2, 4, 36352>, 6, 8, 36352},
             {stream::b64enc_stream<12, 8, 2, 4, 36352>, 12, 8, 36352}, {stream::b64enc_stream<8, 8, 2, 3, 57344>, 8, 8, 57344},
             {stream::b64enc_stream<3, 8, -1, 4>, 3, 8, 0}, {stream::b64enc_stream<3, 8, 2, 4, 0, true>, 3, 8, 0}, {stream::b64enc_stream<3, 8, 4, 4>, 3, 8, 0}};
-        static int occ_v[16];
+        static int occ_v[24];
         const int nv = (int)(sizeof kStream / sizeof *kStream);
         // tiny batches (a single render): the all-arithmetic build, which has no table to fill
         const bool tiny = variant == 0 && L.max_tiles <= 32;
         const StreamVariant &sv = kStream[tiny ? 4 : (variant < nv ? variant : 0)];
         const int threads = 32 * (1 + sv.consumers);
         const size_t dyn = sv.ring ? (size_t)sv.ring : (size_t)sv.stages * stream::kStageStride;
-        static bool attr_set[16];
+        static bool attr_set[64][24];  // per device and variant: the opt-in is a per-device attribute
         const int vi = (int)(&sv - kStream);
-        if (!attr_set[vi]) {
+        int dev = 0;
+        e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        if (dev >= 0 && dev < 64 && !attr_set[dev][vi]) {
             e = cudaFuncSetAttribute(sv.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
             if (e != cudaSuccess) return e;
-            attr_set[vi] = true;
+            attr_set[dev][vi] = true;
         }
         if (occ_v[vi] == 0) {
             int occ = 0;
@@ -1456,9 +1459,17 @@ cudaError_t launch_b64dec_run(const char *d_in, const int64_t *d_in_off, int64_t
         const DecVariant &dv = kDec[dec_variant < nv ? dec_variant : 0];
         const int threads = 32 * (1 + dv.consumers);
         const size_t dyn = (size_t)dv.stages * stream::kDecStageStride;
-        if (g_occ_dec == 0) {
+        // the dynamic-shared-memory opt-in is a per-device function attribute
+        static bool dec_attr_set[64];
+        int dev = 0;
+        e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        if (dev >= 0 && dev < 64 && !dec_attr_set[dev]) {
             e = cudaFuncSetAttribute(dv.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
             if (e != cudaSuccess) return e;
+            dec_attr_set[dev] = true;
+        }
+        if (g_occ_dec == 0) {
             int occ = 0;
             e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dv.fn, threads, dyn);
             if (e != cudaSuccess) return e;
