@@ -229,7 +229,11 @@ def main():
     torch.cuda.set_device(local_rank)
     distributed = world > 1
     if distributed:
-        os.environ["NCCL_DEBUG"] = os.environ.get("KVEDGE_NCCL_DEBUG", "WARN")  # keep stdout to the one JSON line
+        # keep stdout to the one JSON line: NCCL prints its version banner there at any debug level
+        if "KVEDGE_NCCL_DEBUG" in os.environ:
+            os.environ["NCCL_DEBUG"] = os.environ["KVEDGE_NCCL_DEBUG"]
+        else:
+            os.environ.pop("NCCL_DEBUG", None)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     from kvedge_b200 import _lib
     _lib.check(_lib.lib().kv_set_device(local_rank))
