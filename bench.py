@@ -218,6 +218,12 @@ def main():
     if args.impl == "reference":
         return run_reference(args)
 
+    # Libraries (NCCL's version banner, for one) write to fd 1; the contract is ONE JSON line on
+    # stdout, so everything but the final print goes to stderr.
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
     import torch.distributed as dist
     from kvedge_b200 import b64
@@ -426,7 +432,9 @@ def main():
         "gpu_launches_note": "per step: plan_count, plan_emit<0>, b64enc_stream (device-timed region)",
         "clocks": clocks,
     }
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    print(json.dumps(line), flush=True)
     if distributed:
         dist.destroy_process_group()
     return 0

@@ -84,7 +84,7 @@ template <int MODE>
 __global__ void __launch_bounds__(kPlanBlock)
 plan_emit(const int64_t *__restrict__ in_off, const int64_t *__restrict__ out_off,
           int64_t n_units, int tile_in, const int *__restrict__ block_sums,
-          int *__restrict__ header, TileDesc *__restrict__ desc,
+          int *__restrict__ header, TileDesc *__restrict__ desc, int max_tiles,
           int64_t *__restrict__ out_len, int64_t *__restrict__ status) {
     __shared__ int total;
     __shared__ int base_sh;
@@ -120,9 +120,12 @@ plan_emit(const int64_t *__restrict__ in_off, const int64_t *__restrict__ out_of
     }
     int first = base_sh + block_excl_scan(cnt, &total);
     if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
-        header[0] = base_sh + total;
+        // A caller that understated total_in_bytes sized the table too small: never write past
+        // it (the batch then comes out truncated, and header[3] says so, but memory stays intact).
+        header[0] = base_sh + total <= max_tiles ? base_sh + total : max_tiles;
         header[1] = 0;  // tile counter and finished-block counter of the consuming kernel
         header[2] = 0;
+        header[3] = base_sh + total > max_tiles ? 1 : 0;
     }
     for (int k = 0; k < cnt; ++k) {
         int64_t s = (int64_t)k * tile_in;
@@ -134,7 +137,7 @@ plan_emit(const int64_t *__restrict__ in_off, const int64_t *__restrict__ out_of
         d.unit = (int32_t)u;
         d.flags = (k == cnt - 1) ? 1 : 0;
         d.pad = 0;
-        desc[first + k] = d;
+        if (first + k < max_tiles) desc[first + k] = d;
     }
 }
 
@@ -1308,10 +1311,10 @@ static cudaError_t plan(const int64_t *d_in_off, const int64_t *d_out_off, int64
     plan_count<<<nb, kPlanBlock, 0, stream>>>(d_in_off, n_units, tile_in, block_sums);
     if (mode == 0)
         plan_emit<0><<<nb, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in,
-                                                    block_sums, header, desc, nullptr, nullptr);
+                                                    block_sums, header, desc, (int)L.max_tiles, nullptr, nullptr);
     else
         plan_emit<1><<<nb, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in,
-                                                    block_sums, header, desc, d_out_len, d_status);
+                                                    block_sums, header, desc, (int)L.max_tiles, d_out_len, d_status);
     return cudaGetLastError();
 }
 
