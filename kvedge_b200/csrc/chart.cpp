@@ -79,7 +79,7 @@ Value resolve_plain(const std::string &s, bool json_numbers) {
             errno = 0;
             unsigned long long mag = strtoull(digits.c_str(), nullptr, base);
             if (errno == 0) {
-                if (json_numbers) return Value::number(neg ? -(double)mag : (double)mag);
+                if (json_numbers) return Value::number(neg && mag ? -(double)mag : (double)mag);  // "-0" is the integer 0
                 if (mag <= (unsigned long long)INT64_MAX) return Value::integer(neg ? -(int64_t)mag : (int64_t)mag);
                 return Value::number(neg ? -(double)mag : (double)mag);
             }
@@ -375,7 +375,12 @@ struct Yaml {
             std::string key;
             if (!key_txt.empty() && key_txt[0] == '"') { size_t e; key = unquote_double(key_txt, &e); }
             else if (!key_txt.empty() && key_txt[0] == '\'') { size_t e; key = unquote_single(key_txt, &e); }
-            else key = key_txt;
+            else {
+                // go-yaml types plain keys too, and sigs.k8s.io/yaml turns them back into strings:
+                // a key written `n` or `yes` reaches the template as "false" / "true"
+                Value kv = resolve_plain(key_txt, false);
+                key = kv.kind == Value::String ? kv.s : (kv.kind == Value::Nil ? key_txt : tmpl::go_print(kv));
+            }
             ++cur;
             (*v.map)[key] = parse_value_after_key(c.substr(kc + 1), ind);
         }
