@@ -151,7 +151,13 @@ struct Yaml {
         for (size_t i = 0; i < s.size(); ++i) {
             char c = s[i];
             if (dq) { if (c == '\\') ++i; else if (c == '"') dq = false; continue; }
-            if (sq) { if (c == '\'') sq = false; continue; }
+            if (sq) {
+                if (c == '\'') {
+                    if (i + 1 < s.size() && s[i + 1] == '\'') ++i;  // '' is an escaped quote
+                    else sq = false;
+                }
+                continue;
+            }
             if (c == '"' && (i == 0 || is_ws(s[i - 1]) || s[i - 1] == ':' || s[i - 1] == '[' || s[i - 1] == ',' || s[i - 1] == '{')) { dq = true; continue; }
             if (c == '\'' && (i == 0 || is_ws(s[i - 1]) || s[i - 1] == '[' || s[i - 1] == ',' || s[i - 1] == '{')) { sq = true; continue; }
             if (c == '#' && (i == 0 || is_ws(s[i - 1]))) return s.substr(0, i);
@@ -379,7 +385,8 @@ struct Yaml {
                 // go-yaml types plain keys too, and sigs.k8s.io/yaml turns them back into strings:
                 // a key written `n` or `yes` reaches the template as "false" / "true"
                 Value kv = resolve_plain(key_txt, false);
-                key = kv.kind == Value::String ? kv.s : (kv.kind == Value::Nil ? key_txt : tmpl::go_print(kv));
+                if (kv.kind == Value::Nil) throw Error("yaml: unsupported map key of type <nil> (line " + std::to_string(cur + 1) + ")");
+                key = kv.kind == Value::String ? kv.s : tmpl::go_print(kv);
             }
             ++cur;
             (*v.map)[key] = parse_value_after_key(c.substr(kc + 1), ind);
@@ -544,11 +551,11 @@ void assign(Value &root, const std::vector<PathElem> &path, const Value &value) 
         bool next_is_index = !last && path[k + 1].is_index;
         Value *slot;
         if (path[k].is_index) {
-            if (cur->kind != Value::ListK) *cur = Value::make_list();
+            if (cur->kind != Value::ListK) throw Error("--set: cannot index into a map with [" + std::to_string(path[k].index) + "]");
             while (cur->list->size() <= path[k].index) cur->list->push_back(Value::nil());
             slot = &(*cur->list)[path[k].index];
         } else {
-            if (cur->kind != Value::MapK) *cur = Value::make_map();
+            if (cur->kind != Value::MapK) throw Error("--set: key \"" + path[k].key + "\" addresses a list, not a map");
             slot = &(*cur->map)[path[k].key];
         }
         if (last) { *slot = value; return; }

@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cctype>
+#include <charconv>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -34,13 +35,11 @@ std::string format_float(double f) {
     if (std::isnan(f)) return "NaN";
     if (std::isinf(f)) return f > 0 ? "+Inf" : "-Inf";
     if (f == 0) return std::signbit(f) ? "-0" : "0";
-    // shortest round-trip digits: try increasing precision
+    // shortest round-trip digits (strconv's 'shortest' mode); printf at growing precision is
+    // not the same thing: it breaks exact ties to even and can need one digit more (2^-24)
     char buf[64];
-    int prec = 1;
-    for (; prec <= 17; ++prec) {
-        snprintf(buf, sizeof buf, "%.*e", prec - 1, f);
-        if (strtod(buf, nullptr) == f) break;
-    }
+    auto tc = std::to_chars(buf, buf + sizeof buf - 1, f, std::chars_format::scientific);
+    *tc.ptr = 0;
     // buf = [-]d.ddddde[+-]XX
     std::string sb(buf);
     bool neg = sb[0] == '-';

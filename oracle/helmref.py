@@ -87,6 +87,8 @@ def _construct(node: yaml.Node, json_numbers: bool) -> Any:
         out: Dict[bytes, Any] = {}
         for k, v in node.value:
             kk = _construct(k, json_numbers)
+            if kk is None:
+                raise ValueError("yaml: unsupported map key of type <nil>")  # sigs.k8s.io/yaml refuses it
             out[gotmpl.go_print(kk) if not isinstance(kk, bytes) else kk] = _construct(v, json_numbers)
         return out
     raise ValueError("unsupported YAML node")
@@ -203,6 +205,8 @@ def _assign(root: Dict[bytes, Any], path: List[Any], value: Any) -> None:
         last = idx == len(path) - 1
         nxt_is_index = (not last) and isinstance(path[idx + 1], int)
         if isinstance(p, int):
+            if not isinstance(cur, list):
+                raise ValueError(f"--set: cannot index into a map with [{p}]")
             while len(cur) <= p:
                 cur.append(None)
             if last:
@@ -212,6 +216,9 @@ def _assign(root: Dict[bytes, Any], path: List[Any], value: Any) -> None:
                     cur[p] = [] if nxt_is_index else {}
                 cur = cur[p]
         else:
+            if not isinstance(cur, dict):
+                # Helm's strvals type-asserts here and panics; both engines refuse the expression
+                raise ValueError(f"--set: key {p!r} addresses a list, not a map")
             k = p.encode("utf-8")
             if last:
                 cur[k] = value
