@@ -487,6 +487,26 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity))
         if (clock64() - t0 > 8000000000ll) __trap();
 }
+// The same on 32-bit shared addresses computed once per kernel (the pointer forms make the
+// compiler rebuild the shared-window address around every call).
+__device__ __forceinline__ void mbar_arrive_a(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_a(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
+    if (mbar_try_wait_a(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait_a(bar, parity))
+        if (clock64() - t0 > 8000000000ll) __trap();
+}
 __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
@@ -723,54 +743,26 @@ b64enc_stream(const uint8_t *__restrict__ in, char *__restrict__ out,
 // ----------------------------------------------------------------------------- decode, streamed
 // Same producer/consumer ring for the inverse transform (what Kubernetes does to
 // Secret.data.userdata before the guest reads it, _helper.tpl:64,73).  A lane takes 16
-// characters and writes 12 bytes.  Characters are mapped two at a time through a
-// 16384-entry shared-memory table indexed by the pair's two 7-bit codes (entry = the 12
-// decoded bits, or 0xFFFF if either character is outside the alphabet), which validates and
-// decodes in one lookup.  Units that are not canonical ('=' anywhere but the very end, CR/LF,
-// foreign characters, length not a multiple of four) are only *flagged* here (status -2);
-// b64dec_slow then re-decodes them with Go's exact semantics.
-constexpr int kDecStageStride = (kDecTileIn + 32 + 15) / 16 * 16;
+// characters and writes 12 bytes.  Every character goes through a shared-memory table that
+// both validates and decodes it.  Units that are not canonical ('=' anywhere but the very
+// end, CR/LF, foreign characters, length not a multiple of four) are only *flagged* here
+// (status -2); b64dec_slow then re-decodes them with Go's exact semantics.
+//
+// The table has one entry per 7-bit character code, replicated across all 32 shared-memory
+// banks (row c = 32 words): lane l always reads word l of a row, so a lookup is one wavefront
+// whatever the text looks like.  (A 16384-entry pair table, one lookup per two characters,
+// measured 4-5 wavefronts per lookup on real base64 text and was dropped.)  It sits at the
+// start of dynamic shared memory with the ring behind it, so that the plain loop may index it
+// with a whole byte: codes 128..255 read ring bytes, harmlessly, and are caught by bad_w.
+__host__ __device__ constexpr int dec_stage_stride(int tile) { return (tile + 32 + 15) / 16 * 16; }
+constexpr int kDecLutBytes = 128 * 32 * 4;
+constexpr uint32_t kDecBadEntry = 0x01000000u;   // survives the 6- and 12-bit shifts of a group
+constexpr uint32_t kDecBadMask = 0xFF000000u;
 
-__device__ __forceinline__ void fill_dec_pair_lut(uint16_t *lut) {
-    for (int i = threadIdx.x; i < 16384; i += blockDim.x) {
-        // byte offset of an entry is (c1 << 8) | (c0 << 1), i.e. index = c1 * 128 + c0
-        const uint32_t c0 = (uint32_t)i & 127u, c1 = (uint32_t)i >> 7;
-        uint32_t v0 = 0x80u, v1 = 0x80u;
-        if (c0 - 65u < 26u) v0 = c0 - 65u;
-        if (c0 - 97u < 26u) v0 = c0 - 71u;
-        if (c0 - 48u < 10u) v0 = c0 + 4u;
-        if (c0 == 43u) v0 = 62u;
-        if (c0 == 47u) v0 = 63u;
-        if (c1 - 65u < 26u) v1 = c1 - 65u;
-        if (c1 - 97u < 26u) v1 = c1 - 71u;
-        if (c1 - 48u < 10u) v1 = c1 + 4u;
-        if (c1 == 43u) v1 = 62u;
-        if (c1 == 47u) v1 = 63u;
-        lut[i] = ((v0 | v1) & 0x80u) ? (uint16_t)0xFFFFu : (uint16_t)((v0 << 6) | v1);
-    }
-}
-
-// Four characters -> 24 decoded bits (first character in the top sextet); bit 15 of *bad is
-// raised if any character is not in the alphabet (or has bit 7 set).
-__device__ __forceinline__ uint32_t decode_word_lut(uint32_t w, const uint16_t *lut, uint32_t *bad) {
-    const char *base = reinterpret_cast<const char *>(lut);
-    const uint32_t o0 = (w & 0x7F00u) | ((w << 1) & 0xFEu);
-    const uint32_t u = w >> 16;
-    const uint32_t o1 = (u & 0x7F00u) | ((u << 1) & 0xFEu);
-    const uint32_t e0 = *reinterpret_cast<const uint16_t *>(base + o0);
-    const uint32_t e1 = *reinterpret_cast<const uint16_t *>(base + o1);
-    *bad |= e0 | e1 | ((w & 0x80808080u) ? 0x8000u : 0u);
-    return (e0 << 12) | e1;
-}
-
-// Alternative table: one entry per 7-bit character code, but every entry replicated across
-// all 32 shared-memory banks (row c = 32 words).  Lane l always reads word l of a row, so a
-// lookup can never bank-conflict, whatever the text looks like; the pair table above costs
-// 4-5 wavefronts per lookup on real base64 text (ncu), this one exactly 1.
 __device__ __forceinline__ void fill_dec_char_lut(uint32_t *lut) {
     for (int i = threadIdx.x; i < 128 * 32; i += blockDim.x) {
         const uint32_t c = (uint32_t)i >> 5;
-        uint32_t v = 0x80000000u;
+        uint32_t v = kDecBadEntry;
         if (c - 65u < 26u) v = c - 65u;
         if (c - 97u < 26u) v = c - 71u;
         if (c - 48u < 10u) v = c + 4u;
@@ -780,8 +772,8 @@ __device__ __forceinline__ void fill_dec_char_lut(uint32_t *lut) {
     }
 }
 
-// lane4 = 4 * lane.  bad_v collects the looked-up words (bit 31 = not in the alphabet), bad_w
-// the raw characters (bit 7 of any byte = not ASCII).
+// General path: lane4 = 4 * lane.  bad_v collects the looked-up words (kDecBadMask bits = not
+// in the alphabet), bad_w the raw characters (bit 7 of any byte = not ASCII).
 __device__ __forceinline__ uint32_t decode_word_char(uint32_t w, const uint32_t *lut, uint32_t lane4,
                                                      uint32_t *bad_v, uint32_t *bad_w) {
     const char *base = reinterpret_cast<const char *>(lut);
@@ -798,19 +790,40 @@ __device__ __forceinline__ uint32_t decode_word_char(uint32_t w, const uint32_t 
     return ((v0 * 64u + v1) * 64u + v2) * 64u + v3;
 }
 
+// Plain loop: three instructions per character -- byte K of w (PRMT), row address
+// byte * 128 + (table + 4 * lane) (one multiply-add), LDS.
+template <int K>
+__device__ __forceinline__ uint32_t dec_lookup(uint32_t w, uint32_t lut_lane) {
+    uint32_t x, a, v;
+    asm("prmt.b32 %0, %1, 0, %2;" : "=r"(x) : "r"(w), "n"(0x4440 + K));
+    asm("mad.lo.u32 %0, %1, 128, %2;" : "=r"(a) : "r"(x), "r"(lut_lane));
+    asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+
+// Four characters -> 24 bits.  The two 12-bit halves carry a bad entry's flag up to bit 24
+// or bit 30, so one OR of both halves per group collects the validity of all four.
+__device__ __forceinline__ uint32_t decode_word_fast(uint32_t w, uint32_t lut_lane, uint32_t *bad_v) {
+    const uint32_t v0 = dec_lookup<0>(w, lut_lane), v1 = dec_lookup<1>(w, lut_lane);
+    const uint32_t v2 = dec_lookup<2>(w, lut_lane), v3 = dec_lookup<3>(w, lut_lane);
+    const uint32_t p0 = v0 * 64u + v1, p1 = v2 * 64u + v3;
+    *bad_v |= p0 | p1;
+    return p0 * 4096u + p1;
+}
+
 // The plain iterations of one stage for one consumer warp: warp-iterations [ow, plain_end) in
 // steps of kConsumerWarps, all 32 lanes full, no padding possible.  WS (0..3) is the word
 // offset and BSH the byte offset of the stage's first character inside its 16-byte chunk;
 // both are compile-time here so that the loop body has no selects or branches.
 template <int WS, bool BSH, int kConsumerWarps>
-__device__ __forceinline__ void decode_plain(const uint8_t *buf, const uint32_t *lut_words, uint32_t *ow_buf,
+__device__ __forceinline__ void decode_plain(const uint8_t *buf, uint32_t lut_lane, uint32_t *ow_buf,
                                              uint8_t *dst, int ow, int plain_end, uint32_t s8, int lane,
                                              uint32_t *bad_v, uint32_t *bad_w) {
-    const uint32_t lane4 = (uint32_t)lane * 4u;
     const uint4 *vp = reinterpret_cast<const uint4 *>(buf + ow + lane * 16);
     uint4 *qp = reinterpret_cast<uint4 *>(dst + ow / 4 * 3) + lane;
     const uint4 *tp = reinterpret_cast<const uint4 *>(ow_buf) + lane;
     uint32_t *sp = ow_buf + lane * 3;
+    uint32_t bv = *bad_v, bw = *bad_w;
     for (; ow < plain_end; ow += 512 * kConsumerWarps, vp += 32 * kConsumerWarps, qp += 24 * kConsumerWarps) {
         const uint4 A = vp[0];
         uint4 B = make_uint4(0, 0, 0, 0);
@@ -826,10 +839,11 @@ __device__ __forceinline__ void decode_plain(const uint8_t *buf, const uint32_t 
             w2 = __funnelshift_r(w2, w3, s8);
             w3 = __funnelshift_r(w3, w4, s8);
         }
-        const uint32_t n0 = decode_word_char(w0, lut_words, lane4, bad_v, bad_w);
-        const uint32_t n1 = decode_word_char(w1, lut_words, lane4, bad_v, bad_w);
-        const uint32_t n2 = decode_word_char(w2, lut_words, lane4, bad_v, bad_w);
-        const uint32_t n3 = decode_word_char(w3, lut_words, lane4, bad_v, bad_w);
+        bw |= w0 | w1 | w2 | w3;
+        const uint32_t n0 = decode_word_fast(w0, lut_lane, &bv);
+        const uint32_t n1 = decode_word_fast(w1, lut_lane, &bv);
+        const uint32_t n2 = decode_word_fast(w2, lut_lane, &bv);
+        const uint32_t n3 = decode_word_fast(w3, lut_lane, &bv);
         sp[0] = __byte_perm(n0, n1, 0x6012);
         sp[1] = __byte_perm(n1, n2, 0x5601);
         sp[2] = __byte_perm(n2, n3, 0x4560);
@@ -837,26 +851,29 @@ __device__ __forceinline__ void decode_plain(const uint8_t *buf, const uint32_t 
         if (lane < 24) *qp = *tp;
         __syncwarp();
     }
+    *bad_v = bv;
+    *bad_w = bw;
 }
 
-// LUTKIND 0: pair table (16384 x u16); 1: bank-replicated character table (128 x 32 x u32).
-template <int kStages, int kConsumerWarps, int MIN_BLOCKS, int LUTKIND>
+// Dynamic shared memory: [character table, kDecLutBytes][ring, kStages * kDecStageStride].
+template <int kStages, int kConsumerWarps, int MIN_BLOCKS, int kTile>
 __global__ void __launch_bounds__(32 * (1 + kConsumerWarps), MIN_BLOCKS)
 b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
               const TileDesc *__restrict__ desc, int *__restrict__ header,
               const int64_t *__restrict__ in_off, int64_t n_units,
               int64_t *__restrict__ out_len, int64_t *__restrict__ status) {
-    extern __shared__ __align__(128) uint8_t ring[];
+    extern __shared__ __align__(128) uint8_t dyn_smem[];
     __shared__ __align__(8) uint64_t full_bar[kStages];
     __shared__ __align__(8) uint64_t empty_bar[kStages];
     __shared__ StageMeta meta[kStages];
-    __shared__ __align__(128) uint32_t lut_words[LUTKIND == 0 ? 8192 : 4096];
     __shared__ __align__(16) uint32_t obuf[kConsumerWarps][96];  // per-warp store transpose
-    uint16_t *lut = reinterpret_cast<uint16_t *>(lut_words);
+    constexpr int kDecStageStride = dec_stage_stride(kTile);
+    static_assert(kStages * kDecStageStride >= kDecLutBytes, "byte-indexed lookups must stay inside the block's shared memory");
+    uint32_t *lut_words = reinterpret_cast<uint32_t *>(dyn_smem);
+    uint8_t *ring = dyn_smem + kDecLutBytes;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (LUTKIND == 0) fill_dec_pair_lut(lut);
-    else fill_dec_char_lut(lut_words);
+    fill_dec_char_lut(lut_words);
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&full_bar[s], 1);
@@ -941,9 +958,13 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
     } else {
         // ------------------------------------------------------------------ consumers
         const int cw = warp - 1;
-        for (uint32_t c = 0;; ++c) {
-            const int s = (int)(c % kStages);
-            mbar_wait(&full_bar[s], (c / kStages) & 1u);
+        const uint32_t lane4 = (uint32_t)lane * 4u;
+        const uint32_t lut_lane = smem_u32(lut_words) + lane4;
+        const uint32_t full_a = smem_u32(full_bar), empty_a = smem_u32(empty_bar);
+        uint32_t *ow_buf = obuf[cw];
+        uint32_t s = 0, ph = 0;
+        for (;;) {
+            mbar_wait_a(full_a + s * 8u, ph);
             const StageMeta m = meta[s];
             if (m.len < 0) break;
             const int len = m.len, unit = m.pad;
@@ -951,31 +972,28 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
             const uint8_t *buf = ring + s * kDecStageStride;
             uint8_t *dst = reinterpret_cast<uint8_t *>(m.dst);
             const uint32_t sh4 = m.sh & 3u, s8 = sh4 * 8;
-            uint32_t bad = 0, bad_v = 0, bad_w = 0;
-            const uint32_t lane4 = (uint32_t)lane * 4u;
+            uint32_t bad_v = 0, bad_w = 0;
             const bool dst16 = (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
-            uint32_t *ow_buf = obuf[cw];
             // Plain iterations (all 32 lanes full, the unit cannot end inside) go through the
             // branch-free templated loop; whatever is left -- at most the stage's last
             // warp-iteration -- takes the general code below.
             int ow0 = cw * 512;
-            if (LUTKIND == 1 && !bytewise && dst16) {
+            if (!bytewise && dst16) {
                 const int plain_len = last_tile ? len - 1 : len;          // iterations with ow + 512 <= plain_len
-                int n_it = plain_len >= ow0 + 512 ? (plain_len - ow0 - 512) / (512 * kConsumerWarps) + 1 : 0;
+                const int n_it = plain_len >= ow0 + 512 ? (int)((uint32_t)(plain_len - ow0 - 512) / (512u * kConsumerWarps)) + 1 : 0;
                 const int plain_end = ow0 + n_it * 512 * kConsumerWarps;  // first ow not handled here
                 if (n_it > 0) {
-                    const uint32_t ws = m.sh >> 2;
-                    const uint8_t *cb = buf + (m.sh & ~15u);               // == buf: m.sh < 16
+                    const uint32_t ws = m.sh >> 2;                         // m.sh < 16
                     if (sh4 == 0) {
-                        if (ws == 0) decode_plain<0, false, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
-                        else if (ws == 1) decode_plain<1, false, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
-                        else if (ws == 2) decode_plain<2, false, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
-                        else decode_plain<3, false, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        if (ws == 0) decode_plain<0, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        else if (ws == 1) decode_plain<1, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        else if (ws == 2) decode_plain<2, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        else decode_plain<3, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
                     } else {
-                        if (ws == 0) decode_plain<0, true, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
-                        else if (ws == 1) decode_plain<1, true, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
-                        else if (ws == 2) decode_plain<2, true, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
-                        else decode_plain<3, true, kConsumerWarps>(cb, lut_words, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        if (ws == 0) decode_plain<0, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        else if (ws == 1) decode_plain<1, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        else if (ws == 2) decode_plain<2, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        else decode_plain<3, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
                     }
                     ow0 = plain_end;
                 }
@@ -1036,16 +1054,10 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                         }
                     out_len[unit] = (int64_t)(m.src - reinterpret_cast<const uint8_t *>(in) - in_off[unit] + off + nvalid) / 4 * 3 - npad;
                 }
-                uint32_t n0, n1, n2, n3;
-                if (LUTKIND == 0) {
-                    n0 = decode_word_lut(w[0], lut, &bad); n1 = decode_word_lut(w[1], lut, &bad);
-                    n2 = decode_word_lut(w[2], lut, &bad); n3 = decode_word_lut(w[3], lut, &bad);
-                } else {
-                    n0 = decode_word_char(w[0], lut_words, lane4, &bad_v, &bad_w);
-                    n1 = decode_word_char(w[1], lut_words, lane4, &bad_v, &bad_w);
-                    n2 = decode_word_char(w[2], lut_words, lane4, &bad_v, &bad_w);
-                    n3 = decode_word_char(w[3], lut_words, lane4, &bad_v, &bad_w);
-                }
+                const uint32_t n0 = decode_word_char(w[0], lut_words, lane4, &bad_v, &bad_w);
+                const uint32_t n1 = decode_word_char(w[1], lut_words, lane4, &bad_v, &bad_w);
+                const uint32_t n2 = decode_word_char(w[2], lut_words, lane4, &bad_v, &bad_w);
+                const uint32_t n3 = decode_word_char(w[3], lut_words, lane4, &bad_v, &bad_w);
                 // 4 x 24 bits (big-endian inside each group) -> 12 bytes in stream order
                 const uint32_t o0 = __byte_perm(n0, n1, 0x6012);
                 const uint32_t o1 = __byte_perm(n1, n2, 0x5601);
@@ -1073,10 +1085,10 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                         if (i < nbytes) q[i] = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
                 }
             }
-            if (LUTKIND != 0) bad = ((bad_v & 0x80000000u) || (bad_w & 0x80808080u)) ? 0x8000u : 0u;
-            if (bad & 0x8000u) status[unit] = -2;  // benign race: every writer stores the same value
+            if ((bad_v & kDecBadMask) || (bad_w & 0x80808080u)) status[unit] = -2;  // benign race: every writer stores the same value
             __syncwarp();
-            if (lane == 0) mbar_arrive(&empty_bar[s]);
+            if (lane == 0) mbar_arrive_a(empty_a + s * 8u);
+            if (++s == kStages) { s = 0; ph ^= 1u; }
         }
     }
 }
@@ -1420,14 +1432,38 @@ cudaError_t launch_b64enc(const uint8_t *d_in, const int64_t *d_in_off, int64_t 
                              scratch_bytes, stream, sm_count);
 }
 
+// The streamed decode kernel's shapes.  Entry 0 is the product; the others are kept for
+// tools/sweep_dec.py (KVEDGE_DEC_VARIANT=n), 100 selects the older load/store kernel.
+using DecKernel = void (*)(const char *, uint8_t *, const TileDesc *, int *, const int64_t *, int64_t,
+                           int64_t *, int64_t *);
+struct DecVariant { DecKernel fn; int stages, consumers, tile; };
+static const DecVariant kDec[] = {
+    {stream::b64dec_stream<3, 8, 4, 16384>, 3, 8, 16384}, {stream::b64dec_stream<2, 8, 4, 16384>, 2, 8, 16384},
+    {stream::b64dec_stream<4, 8, 4, 12288>, 4, 8, 12288}, {stream::b64dec_stream<6, 8, 4, 8192>, 6, 8, 8192},
+    {stream::b64dec_stream<4, 8, 4, 8192>, 4, 8, 8192},   {stream::b64dec_stream<3, 4, 4, 16384>, 3, 4, 16384},
+    {stream::b64dec_stream<5, 8, 4, 8192>, 5, 8, 8192},   {stream::b64dec_stream<3, 8, 4, 12288>, 3, 8, 12288}};
+
+static int dec_variant() {
+    static int v = -1;
+    if (v < 0) {
+        const char *e = getenv("KVEDGE_DEC_VARIANT");
+        int x = e ? atoi(e) : 0;
+        if (x < 0 || (x < 100 && x >= (int)(sizeof kDec / sizeof *kDec))) x = 0;
+        v = x;
+    }
+    return v;
+}
+
+int dec_tile_in() { return dec_variant() < 100 ? kDec[dec_variant()].tile : kDecTileIn; }
+
 cudaError_t launch_b64dec(const char *d_in, const int64_t *d_in_off, int64_t n_units,
                           int64_t total_in_bytes, uint8_t *d_out, const int64_t *d_out_off,
                           int64_t *d_out_len, int64_t *d_status, void *d_scratch,
                           size_t scratch_bytes, cudaStream_t stream, int sm_count) {
     if (n_units <= 0) return cudaSuccess;
-    ScratchLayout L = scratch_layout(n_units, total_in_bytes, kDecTileIn);
+    ScratchLayout L = scratch_layout(n_units, total_in_bytes, dec_tile_in());
     if (scratch_bytes < L.total) return cudaErrorInvalidValue;
-    cudaError_t e = plan(d_in_off, d_out_off, n_units, kDecTileIn, 1, L, d_scratch, d_out_len,
+    cudaError_t e = plan(d_in_off, d_out_off, n_units, dec_tile_in(), 1, L, d_scratch, d_out_len,
                          d_status, stream);
     if (e != cudaSuccess) return e;
     return launch_b64dec_run(d_in, d_in_off, n_units, total_in_bytes, d_out, d_out_off, d_out_len,
@@ -1441,27 +1477,15 @@ cudaError_t launch_b64dec_run(const char *d_in, const int64_t *d_in_off, int64_t
                               int64_t *d_out_len, int64_t *d_status, void *d_scratch,
                               size_t scratch_bytes, cudaStream_t stream, int sm_count) {
     if (n_units <= 0) return cudaSuccess;
-    ScratchLayout L = scratch_layout(n_units, total_in_bytes, kDecTileIn);
+    ScratchLayout L = scratch_layout(n_units, total_in_bytes, dec_tile_in());
     if (scratch_bytes < L.total) return cudaErrorInvalidValue;
     cudaError_t e;
-    static int dec_variant = -1;
-    if (dec_variant < 0) {  // KVEDGE_DEC_VARIANT=100 selects the older load/store kernel (tools/)
-        const char *v = getenv("KVEDGE_DEC_VARIANT");
-        dec_variant = v ? atoi(v) : 0;
-        if (dec_variant < 0) dec_variant = 0;
-    }
+    const int variant = dec_variant();
     char *base = static_cast<char *>(d_scratch);
-    if (dec_variant < 100) {
-        using DecKernel = void (*)(const char *, uint8_t *, const TileDesc *, int *, const int64_t *, int64_t,
-                                   int64_t *, int64_t *);
-        struct DecVariant { DecKernel fn; int stages, consumers; };
-        static const DecVariant kDec[] = {{stream::b64dec_stream<3, 8, 4, 1>, 3, 8}, {stream::b64dec_stream<3, 8, 3, 0>, 3, 8},
-                                          {stream::b64dec_stream<4, 8, 4, 1>, 4, 8}, {stream::b64dec_stream<2, 8, 5, 1>, 2, 8},
-                                          {stream::b64dec_stream<3, 12, 3, 1>, 3, 12}};
-        const int nv = (int)(sizeof kDec / sizeof *kDec);
-        const DecVariant &dv = kDec[dec_variant < nv ? dec_variant : 0];
+    if (variant < 100) {
+        const DecVariant &dv = kDec[variant];
         const int threads = 32 * (1 + dv.consumers);
-        const size_t dyn = (size_t)dv.stages * stream::kDecStageStride;
+        const size_t dyn = (size_t)stream::kDecLutBytes + (size_t)dv.stages * stream::dec_stage_stride(dv.tile);
         // the dynamic-shared-memory opt-in is a per-device function attribute
         static bool dec_attr_set[64];
         int dev = 0;

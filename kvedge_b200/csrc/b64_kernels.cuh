@@ -11,8 +11,11 @@ namespace kvedge {
 constexpr int kEncTileIn = 12288;
 constexpr int kEncTileOut = kEncTileIn / 3 * 4;
 // Input characters per decode tile (one ring stage of the streamed decode kernel).
+// The default; dec_tile_in() is what the planners and the kernel actually use (a diagnostic
+// variant may pick another size, never below kMinTileIn).
 constexpr int kDecTileIn = 16384;
-constexpr int kMinTileIn = kDecTileIn < kEncTileIn ? kDecTileIn : kEncTileIn;  // sizes the scratch
+constexpr int kMinTileIn = 8192;  // sizes the scratch
+int dec_tile_in();
 constexpr int kThreads = 256;
 constexpr int kPlanBlock = 1024;  // units per block in the plan kernels
 

@@ -166,7 +166,7 @@ int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *ou
     const int64_t in_bytes = iend - ibeg, out_bytes = oend - obeg;
     // keep each unit's alignment (mod 16) identical on the device and on the host side
     const int64_t ishift = ibeg & 15, oshift = obeg & 15;
-    const int tile = mode == 0 ? kvedge::kEncTileIn : kvedge::kDecTileIn;
+    const int tile = mode == 0 ? kvedge::kEncTileIn : kvedge::dec_tile_in();
     const kvedge::ScratchLayout L = kvedge::scratch_layout(n, in_bytes + ishift, tile);
     const size_t off_in = 0, off_out = (size_t)(n + 1) * 8, off_len = off_out + (size_t)(n + 1) * 8;
     const size_t off_status = off_len + (size_t)n * 8;
@@ -347,7 +347,7 @@ int kv_b64dec_batch_dev(const char *d_in, const int64_t *d_in_off, int64_t n_uni
     if (n_units == 0) return KV_OK;
     if (!d_in_off || !d_out_off || !d_scratch || !d_out_len || !d_status)
         return fail(KV_EINVAL, "null pointer");
-    size_t need = kvedge::scratch_layout(n_units, total_in_bytes, kvedge::kDecTileIn).total;
+    size_t need = kvedge::scratch_layout(n_units, total_in_bytes, kvedge::dec_tile_in()).total;
     if (scratch_bytes < need)
         return fail(KV_ENOMEM, "scratch too small: %zu < %zu (kv_b64_scratch_bytes)", scratch_bytes, need);
     int sms = 0;
