@@ -855,41 +855,146 @@ __device__ __forceinline__ void decode_plain(const uint8_t *buf, uint32_t lut_la
     *bad_w = bw;
 }
 
-// Dynamic shared memory: [character table, kDecLutBytes][ring, kStages * kDecStageStride].
-template <int kStages, int kConsumerWarps, int MIN_BLOCKS, int kTile>
-__global__ void __launch_bounds__(32 * (1 + kConsumerWarps), MIN_BLOCKS)
+// What the producer tells the consumers about a stage.  The first 16 bytes are all the hot
+// path reads.
+struct __align__(16) DecMeta {
+    uint8_t *dst;        // where this stage's bytes go
+    int len;             // characters in this stage; < 0: no more work
+    uint32_t info;       // bits 0-3: offset of the first character in the stage buffer;
+                         // bit 8: last tile of its unit; bit 9: byte-wise stage (no bulk copy)
+    const uint8_t *src;  // global address of the first character (byte-wise stages, out_len)
+    int unit;
+    int pad;
+};
+
+// A shared address the compiler cannot rematerialise (it would otherwise rebuild the
+// shared-window base around every barrier operation).
+__device__ __forceinline__ uint32_t pinned_smem_u32(const void *p) {
+    uint32_t a = smem_u32(p), r;
+    asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(a));
+    return r;
+}
+
+// The last, partial warp-iteration of a stage in the common layout (bulk-copied stage,
+// 16-byte aligned destination): all lanes decode -- lanes past the end decode filler -- the
+// 12-byte pieces are transposed through shared memory like in the plain loop, and the
+// iteration's nb_total bytes leave as 16-byte stores plus one ragged piece.
+__device__ __forceinline__ void decode_tail(const uint8_t *buf, uint32_t sh, uint32_t lut_lane, uint32_t *ow_buf,
+                                            uint8_t *dst, int ow, int len, bool last_tile, int lane,
+                                            uint32_t *bad_v, uint32_t *bad_w, int *npad_out) {
+    const int off = ow + lane * 16;
+    int nvalid = len - off;
+    nvalid = nvalid < 0 ? 0 : (nvalid > 16 ? 16 : nvalid);   // a multiple of 4
+    const uint4 *vp = reinterpret_cast<const uint4 *>(buf + off);
+    uint4 A = make_uint4(0, 0, 0, 0), B = A;
+    if (nvalid > 0) { A = vp[0]; B = vp[1]; }   // lanes past the end must not read past the tile's slot
+    uint32_t w[5];
+    const uint32_t ws = sh >> 2, s8 = (sh & 3u) * 8;
+    if (ws == 0) { w[0] = A.x; w[1] = A.y; w[2] = A.z; w[3] = A.w; w[4] = B.x; }
+    else if (ws == 1) { w[0] = A.y; w[1] = A.z; w[2] = A.w; w[3] = B.x; w[4] = B.y; }
+    else if (ws == 2) { w[0] = A.z; w[1] = A.w; w[2] = B.x; w[3] = B.y; w[4] = B.z; }
+    else { w[0] = A.w; w[1] = B.x; w[2] = B.y; w[3] = B.z; w[4] = B.w; }
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        w[g] = __funnelshift_r(w[g], w[g + 1], s8);
+        if (g * 4 >= nvalid) w[g] = 0x41414141u;
+    }
+    int npad = 0;
+    if (last_tile && nvalid > 0 && off + nvalid == len) {
+        // '=' padding is legal only in the last quantum of the unit
+        const int gq = (nvalid >> 2) - 1;
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+            if (g == gq && (w[g] >> 24) == 0x3Du) {
+                npad = 1;
+                w[g] = (w[g] & 0x00FFFFFFu) | 0x41000000u;
+                if (((w[g] >> 16) & 0xFFu) == 0x3Du) {
+                    npad = 2;
+                    w[g] = (w[g] & 0xFF00FFFFu) | 0x00410000u;
+                }
+            }
+    }
+    *bad_w |= w[0] | w[1] | w[2] | w[3];
+    const uint32_t n0 = decode_word_fast(w[0], lut_lane, bad_v);
+    const uint32_t n1 = decode_word_fast(w[1], lut_lane, bad_v);
+    const uint32_t n2 = decode_word_fast(w[2], lut_lane, bad_v);
+    const uint32_t n3 = decode_word_fast(w[3], lut_lane, bad_v);
+    ow_buf[lane * 3 + 0] = __byte_perm(n0, n1, 0x6012);
+    ow_buf[lane * 3 + 1] = __byte_perm(n1, n2, 0x5601);
+    ow_buf[lane * 3 + 2] = __byte_perm(n2, n3, 0x4560);
+    __syncwarp();
+    const int owner = (len - ow - 1) >> 4;                     // lane holding the last quantum
+    npad = __shfl_sync(0xffffffffu, npad, owner);
+    *npad_out = npad;
+    const int nb_total = (len - ow) / 4 * 3 - npad;            // 1..384
+    const int r = nb_total - lane * 16;                        // bytes of this lane's 16-byte piece
+    uint8_t *q = dst + ow / 4 * 3 + lane * 16;
+    const uint32_t *t = ow_buf + lane * 4;
+    if (lane < 24 && r >= 16) {
+        *reinterpret_cast<uint4 *>(q) = *reinterpret_cast<const uint4 *>(t);
+    } else if (lane < 24 && r > 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            if (r >= 4 * (k + 1)) reinterpret_cast<uint32_t *>(q)[k] = t[k];
+        const uint32_t lastw = t[r >> 2];
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            if (k < (r & 3)) q[(r & ~3) + k] = (uint8_t)(lastw >> (8 * k));
+    }
+    __syncwarp();
+}
+
+// One block per SM holds kGroups independent pipelines -- each a producer warp, its own ring
+// of kStages tiles and kConsumerWarps consumer warps -- around ONE character table.
+// Dynamic shared memory: [table, kDecLutBytes][kGroups rings of kStages * stride bytes].
+//
+// kRing == 0: every tile gets one of kStages fixed slots of kTile (+slack) bytes.  kRing > 0:
+// the group's ring is kRing bytes handed out by size, so that a 3 KB cloud-init text does not
+// hold a 16 KB slot and the next big tile can load while the current one is still being
+// decoded; kStages is then only the number of tiles that may be in flight.
+template <int kGroups, int kStages, int kConsumerWarps, int MIN_BLOCKS, int kTile, int kRing = 0>
+__global__ void __launch_bounds__(32 * kGroups * (1 + kConsumerWarps), MIN_BLOCKS)
 b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
               const TileDesc *__restrict__ desc, int *__restrict__ header,
               const int64_t *__restrict__ in_off, int64_t n_units,
               int64_t *__restrict__ out_len, int64_t *__restrict__ status) {
-    extern __shared__ __align__(128) uint8_t dyn_smem[];
-    __shared__ __align__(8) uint64_t full_bar[kStages];
-    __shared__ __align__(8) uint64_t empty_bar[kStages];
-    __shared__ StageMeta meta[kStages];
-    __shared__ __align__(16) uint32_t obuf[kConsumerWarps][96];  // per-warp store transpose
+    constexpr int kGroupWarps = 1 + kConsumerWarps;
     constexpr int kDecStageStride = dec_stage_stride(kTile);
-    static_assert(kStages * kDecStageStride >= kDecLutBytes, "byte-indexed lookups must stay inside the block's shared memory");
+    constexpr int kGroupBytes = kRing > 0 ? kRing : kStages * kDecStageStride;
+    static_assert(kGroupBytes >= kDecLutBytes, "byte-indexed lookups must stay inside the block's shared memory");
+    static_assert(kTile % 512 == 0, "a stage is a whole number of warp-iterations");
+    static_assert(kRing == 0 || (kRing % 16 == 0 && kRing >= kTile + 64), "ring must hold one full tile");
+    extern __shared__ __align__(128) uint8_t dyn_smem[];
+    __shared__ __align__(8) uint64_t full_bar[kGroups][kStages];
+    __shared__ __align__(8) uint64_t empty_bar[kGroups][kStages];
+    __shared__ DecMeta meta[kGroups][kStages];
+    __shared__ uint32_t ring_start[kGroups][kStages];  // producer only: where each in-flight tile starts
+    __shared__ __align__(16) uint32_t obuf[kGroups * kConsumerWarps][96];  // per-warp store transpose
     uint32_t *lut_words = reinterpret_cast<uint32_t *>(dyn_smem);
-    uint8_t *ring = dyn_smem + kDecLutBytes;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int grp = warp / kGroupWarps, role = warp % kGroupWarps;
+    uint8_t *ring = dyn_smem + kDecLutBytes + grp * kGroupBytes;
     fill_dec_char_lut(lut_words);
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kStages; ++s) {
-            mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], kConsumerWarps);
-        }
+        for (int g = 0; g < kGroups; ++g)
+            for (int s = 0; s < kStages; ++s) {
+                mbar_init(&full_bar[g][s], 1);
+                mbar_init(&empty_bar[g][s], kConsumerWarps);
+            }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    const uint32_t full_a = pinned_smem_u32(&full_bar[grp][0]), empty_a = pinned_smem_u32(&empty_bar[grp][0]);
 
-    if (warp == 0) {
+    if (role == 0) {
         // ------------------------------------------------------------------ producer
         const int n_tiles = header[0];
         const int64_t in_end = in_off[n_units];
-        const int n_blocks = (int)gridDim.x;
-        uint32_t c = 0;
-        int base = (int)blockIdx.x, count = base < n_tiles ? 1 : 0;
+        const int n_groups = (int)gridDim.x * kGroups;
+        uint32_t c = 0;                  // tiles issued so far; tile c uses barrier pair c % kStages
+        uint32_t head = 0, waited = 0;   // kRing: allocation point; tiles [waited, c) are in flight
+        int base = (int)blockIdx.x * kGroups + grp, count = base < n_tiles ? 1 : 0;
         while (count > 0) {
             int4 d0 = make_int4(0, 0, 0, 0), d1 = make_int4(0, 0, 0, 0);
             if (lane < count) {
@@ -900,9 +1005,9 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
             int nbase = 0, ncount = 0;
             if (lane == 0) {
                 int rem = n_tiles - (base + count);
-                int g = rem / (2 * n_blocks);
+                int g = rem / (2 * n_groups);
                 g = g < 1 ? 1 : (g > kGrabMax ? kGrabMax : g);
-                nbase = atomicAdd(&header[1], g) + n_blocks;
+                nbase = atomicAdd(&header[1], g) + n_groups;
                 ncount = nbase < n_tiles ? (n_tiles - nbase < g ? n_tiles - nbase : g) : 0;
             }
             for (int t = 0; t < count; ++t) {
@@ -919,23 +1024,49 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                 uint8_t *dst = out + out_pos;
                 const bool dst4 = (reinterpret_cast<uintptr_t>(dst) & 3u) == 0;
                 const bool bulk_ok = in_pos >= 16 && in_pos + len + 16 <= in_end && dst4;
-                const int s = (int)(c % kStages);
-                mbar_wait(&empty_bar[s], ((c / kStages) & 1u) ^ 1u);
+                const uint32_t s = c % kStages;
                 const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
-                StageMeta m;
-                m.dst = reinterpret_cast<char *>(dst);
-                m.src = src;
+                uint32_t boff = s * kDecStageStride;
+                if (kRing == 0) {
+                    mbar_wait_a(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
+                } else {
+                    // the barrier pair itself: tile c - kStages must be finished
+                    while (waited + kStages <= c) {
+                        mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                        ++waited;
+                    }
+                    // room for this tile (+ the 16-byte chunk a lane may read past its last character)
+                    const uint32_t need = (sh + (uint32_t)len + 32u + 15u) & ~15u;
+                    for (;;) {
+                        if (waited == c) { head = 0; break; }                     // nothing in flight
+                        const uint32_t tail = ring_start[grp][waited % kStages];  // oldest tile in flight
+                        if (head > tail) {                                        // in flight: [tail, head)
+                            if (head + need <= (uint32_t)kRing) break;
+                            if (need <= tail) { head = 0; break; }                // wrap to the front
+                        } else if (head + need <= tail) {                         // in flight: [tail, end) + [0, head)
+                            break;
+                        }
+                        mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                        ++waited;
+                    }
+                    boff = head;
+                    ring_start[grp][s] = head;
+                    head += need;
+                }
+                DecMeta m;
+                m.dst = dst;
                 m.len = len;
-                m.sh = sh;
-                m.flags = (tflags & 1) | (bulk_ok ? 0 : 2);   // bit0: last tile of its unit
-                m.pad = unit;
-                meta[s] = m;
+                m.info = sh | ((uint32_t)(tflags & 1) << 8) | (bulk_ok ? 0u : 0x200u) | (boff << 12);  // boff is a multiple of 16
+                m.src = src;
+                m.unit = unit;
+                m.pad = 0;
+                meta[grp][s] = m;
                 if (bulk_ok) {
                     const uint32_t bytes = (sh + (uint32_t)len + 15u) & ~15u;
-                    mbar_arrive_expect_tx(&full_bar[s], bytes);
-                    bulk_g2s(ring + s * kDecStageStride, src - sh, bytes, &full_bar[s]);
+                    mbar_arrive_expect_tx(&full_bar[grp][s], bytes);
+                    bulk_g2s(ring + boff, src - sh, bytes, &full_bar[grp][s]);
                 } else {
-                    mbar_arrive(&full_bar[s]);
+                    mbar_arrive(&full_bar[grp][s]);
                 }
                 ++c;
             }
@@ -944,12 +1075,19 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
             count = __shfl_sync(0xffffffffu, ncount, 0);
         }
         if (lane == 0) {
-            const int s = (int)(c % kStages);
-            mbar_wait(&empty_bar[s], ((c / kStages) & 1u) ^ 1u);
-            meta[s].len = -1;
-            mbar_arrive(&full_bar[s]);
+            const uint32_t s = c % kStages;
+            if (kRing == 0) {
+                mbar_wait_a(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
+            } else {
+                while (waited + kStages <= c) {
+                    mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                    ++waited;
+                }
+            }
+            meta[grp][s].len = -1;
+            mbar_arrive(&full_bar[grp][s]);
             __threadfence();
-            if (atomicAdd(&header[2], 1) == n_blocks - 1) {
+            if (atomicAdd(&header[2], 1) == n_groups - 1) {
                 header[1] = 0;
                 header[2] = 0;
                 __threadfence();
@@ -957,33 +1095,34 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
         }
     } else {
         // ------------------------------------------------------------------ consumers
-        const int cw = warp - 1;
+        const int cw = role - 1;
         const uint32_t lane4 = (uint32_t)lane * 4u;
-        const uint32_t lut_lane = smem_u32(lut_words) + lane4;
-        const uint32_t full_a = smem_u32(full_bar), empty_a = smem_u32(empty_bar);
-        uint32_t *ow_buf = obuf[cw];
+        const uint32_t lut_lane = pinned_smem_u32(lut_words) + lane4;
+        uint32_t *ow_buf = obuf[grp * kConsumerWarps + cw];
+        const DecMeta *gmeta = meta[grp];
         uint32_t s = 0, ph = 0;
         for (;;) {
             mbar_wait_a(full_a + s * 8u, ph);
-            const StageMeta m = meta[s];
-            if (m.len < 0) break;
-            const int len = m.len, unit = m.pad;
-            const bool last_tile = (m.flags & 1) != 0, bytewise = (m.flags & 2) != 0;
-            const uint8_t *buf = ring + s * kDecStageStride;
-            uint8_t *dst = reinterpret_cast<uint8_t *>(m.dst);
-            const uint32_t sh4 = m.sh & 3u, s8 = sh4 * 8;
+            const int4 hot = *reinterpret_cast<const int4 *>(&gmeta[s]);
+            const int len = hot.z;
+            if (len < 0) break;
+            const uint32_t info = (uint32_t)hot.w, sh = info & 15u;
+            const bool last_tile = (info & 0x100u) != 0, bytewise = (info & 0x200u) != 0;
+            const uint8_t *buf = ring + ((info >> 12) & ~15u);
+            uint8_t *dst = reinterpret_cast<uint8_t *>(((uint64_t)(uint32_t)hot.y << 32) | (uint32_t)hot.x);
+            const uint32_t sh4 = sh & 3u, s8 = sh4 * 8;
             uint32_t bad_v = 0, bad_w = 0;
             const bool dst16 = (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
             // Plain iterations (all 32 lanes full, the unit cannot end inside) go through the
-            // branch-free templated loop; whatever is left -- at most the stage's last
-            // warp-iteration -- takes the general code below.
+            // branch-free templated loop; the stage's last warp-iteration takes decode_tail;
+            // byte-wise stages and unaligned destinations take the general code below.
             int ow0 = cw * 512;
             if (!bytewise && dst16) {
                 const int plain_len = last_tile ? len - 1 : len;          // iterations with ow + 512 <= plain_len
                 const int n_it = plain_len >= ow0 + 512 ? (int)((uint32_t)(plain_len - ow0 - 512) / (512u * kConsumerWarps)) + 1 : 0;
                 const int plain_end = ow0 + n_it * 512 * kConsumerWarps;  // first ow not handled here
                 if (n_it > 0) {
-                    const uint32_t ws = m.sh >> 2;                         // m.sh < 16
+                    const uint32_t ws = sh >> 2;
                     if (sh4 == 0) {
                         if (ws == 0) decode_plain<0, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
                         else if (ws == 1) decode_plain<1, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
@@ -996,6 +1135,15 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                         else decode_plain<3, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
                     }
                     ow0 = plain_end;
+                }
+                if (ow0 < len) {   // this warp owns the stage's last warp-iteration
+                    int npad = 0;
+                    decode_tail(buf, sh, lut_lane, ow_buf, dst, ow0, len, last_tile, lane, &bad_v, &bad_w, &npad);
+                    if (last_tile && lane == 0) {
+                        const int unit = gmeta[s].unit;
+                        out_len[unit] = (int64_t)(gmeta[s].src - reinterpret_cast<const uint8_t *>(in) - in_off[unit] + len) / 4 * 3 - npad;
+                    }
+                    ow0 = len;
                 }
             }
             for (int ow = ow0; ow < len; ow += 512 * kConsumerWarps) {   // warp-uniform loop
@@ -1010,10 +1158,10 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                     const uint4 *vp = reinterpret_cast<const uint4 *>(buf + off);
                     const uint4 A = vp[0];
                     w[0] = A.x; w[1] = A.y; w[2] = A.z; w[3] = A.w;
-                    if (m.sh) {
+                    if (sh) {
                         const uint4 B = vp[1];
                         uint32_t w4 = B.x;
-                        const uint32_t ws = m.sh >> 2;
+                        const uint32_t ws = sh >> 2;
                         if (ws == 1) { w[0] = A.y; w[1] = A.z; w[2] = A.w; w[3] = B.x; w4 = B.y; }
                         else if (ws == 2) { w[0] = A.z; w[1] = A.w; w[2] = B.x; w[3] = B.y; w4 = B.z; }
                         else if (ws == 3) { w[0] = A.w; w[1] = B.x; w[2] = B.y; w[3] = B.z; w4 = B.w; }
@@ -1030,7 +1178,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                             if (g * 4 >= nvalid) w[g] = 0x41414141u;
                     }
                 } else if (active) {
-                    const uint8_t *p = m.src + off;
+                    const uint8_t *p = gmeta[s].src + off;
 #pragma unroll
                     for (int i = 0; i < 16; ++i)
                         if (i < nvalid) {
@@ -1052,7 +1200,8 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                                 w[g] = (w[g] & 0xFF00FFFFu) | 0x00410000u;
                             }
                         }
-                    out_len[unit] = (int64_t)(m.src - reinterpret_cast<const uint8_t *>(in) - in_off[unit] + off + nvalid) / 4 * 3 - npad;
+                    const int unit = gmeta[s].unit;
+                    out_len[unit] = (int64_t)(gmeta[s].src - reinterpret_cast<const uint8_t *>(in) - in_off[unit] + off + nvalid) / 4 * 3 - npad;
                 }
                 const uint32_t n0 = decode_word_char(w[0], lut_words, lane4, &bad_v, &bad_w);
                 const uint32_t n1 = decode_word_char(w[1], lut_words, lane4, &bad_v, &bad_w);
@@ -1064,18 +1213,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                 const uint32_t o2 = __byte_perm(n2, n3, 0x4560);
                 uint8_t *q = dst + off / 4 * 3;
                 const int nbytes = nq * 3 - npad;
-                // A full warp-iteration (32 lanes x 12 bytes = 384 contiguous bytes) is transposed
-                // through shared memory so that 24 lanes can store 16 bytes each: 12 whole sectors
-                // instead of 36 byte-masked ones.
-                if (dst16 && __all_sync(0xffffffffu, !bytewise && nbytes == 12)) {
-                    ow_buf[lane * 3 + 0] = o0;
-                    ow_buf[lane * 3 + 1] = o1;
-                    ow_buf[lane * 3 + 2] = o2;
-                    __syncwarp();
-                    if (lane < 24)
-                        reinterpret_cast<uint4 *>(dst + ow / 4 * 3)[lane] = reinterpret_cast<const uint4 *>(ow_buf)[lane];
-                    __syncwarp();
-                } else if (!bytewise && nbytes == 12) {
+                if (!bytewise && nbytes == 12) {
                     uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
                     q4[0] = o0; q4[1] = o1; q4[2] = o2;
                 } else if (active) {
@@ -1085,7 +1223,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                         if (i < nbytes) q[i] = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
                 }
             }
-            if ((bad_v & kDecBadMask) || (bad_w & 0x80808080u)) status[unit] = -2;  // benign race: every writer stores the same value
+            if ((bad_v & kDecBadMask) || (bad_w & 0x80808080u)) status[gmeta[s].unit] = -2;  // benign race: every writer stores the same value
             __syncwarp();
             if (lane == 0) mbar_arrive_a(empty_a + s * 8u);
             if (++s == kStages) { s = 0; ph ^= 1u; }
@@ -1436,12 +1574,15 @@ cudaError_t launch_b64enc(const uint8_t *d_in, const int64_t *d_in_off, int64_t 
 // tools/sweep_dec.py (KVEDGE_DEC_VARIANT=n), 100 selects the older load/store kernel.
 using DecKernel = void (*)(const char *, uint8_t *, const TileDesc *, int *, const int64_t *, int64_t,
                            int64_t *, int64_t *);
-struct DecVariant { DecKernel fn; int stages, consumers, tile; };
+struct DecVariant { DecKernel fn; int groups, stages, consumers, tile, ring; };
 static const DecVariant kDec[] = {
-    {stream::b64dec_stream<3, 8, 4, 16384>, 3, 8, 16384}, {stream::b64dec_stream<2, 8, 4, 16384>, 2, 8, 16384},
-    {stream::b64dec_stream<4, 8, 4, 12288>, 4, 8, 12288}, {stream::b64dec_stream<6, 8, 4, 8192>, 6, 8, 8192},
-    {stream::b64dec_stream<4, 8, 4, 8192>, 4, 8, 8192},   {stream::b64dec_stream<3, 4, 4, 16384>, 3, 4, 16384},
-    {stream::b64dec_stream<5, 8, 4, 8192>, 5, 8, 8192},   {stream::b64dec_stream<3, 8, 4, 12288>, 3, 8, 12288}};
+    {stream::b64dec_stream<5, 8, 5, 1, 16384, 40448>, 5, 8, 5, 16384, 40448},  // product
+    {stream::b64dec_stream<1, 3, 8, 4, 16384>, 1, 3, 8, 16384, 0},             // one pipeline per block, 3 blocks/SM
+    {stream::b64dec_stream<6, 2, 4, 1, 16384>, 6, 2, 4, 16384, 0},             // grouped, fixed slots
+    {stream::b64dec_stream<5, 4, 5, 1, 16384, 40960>, 5, 4, 5, 16384, 40960},
+    {stream::b64dec_stream<6, 4, 4, 1, 16384, 34256>, 6, 4, 4, 16384, 34256},
+    {stream::b64dec_stream<5, 8, 4, 1, 16384, 40448>, 5, 8, 4, 16384, 40448},
+    {stream::b64dec_stream<4, 8, 6, 1, 16384, 50688>, 4, 8, 6, 16384, 50688}};
 
 static int dec_variant() {
     static int v = -1;
@@ -1484,8 +1625,8 @@ cudaError_t launch_b64dec_run(const char *d_in, const int64_t *d_in_off, int64_t
     char *base = static_cast<char *>(d_scratch);
     if (variant < 100) {
         const DecVariant &dv = kDec[variant];
-        const int threads = 32 * (1 + dv.consumers);
-        const size_t dyn = (size_t)stream::kDecLutBytes + (size_t)dv.stages * stream::dec_stage_stride(dv.tile);
+        const int threads = 32 * dv.groups * (1 + dv.consumers);
+        const size_t dyn = (size_t)stream::kDecLutBytes + (size_t)dv.groups * (dv.ring ? (size_t)dv.ring : (size_t)dv.stages * stream::dec_stage_stride(dv.tile));
         // the dynamic-shared-memory opt-in is a per-device function attribute
         static bool dec_attr_set[64];
         int dev = 0;
@@ -1503,7 +1644,7 @@ cudaError_t launch_b64dec_run(const char *d_in, const int64_t *d_in_off, int64_t
             g_occ_dec = occ > 0 ? occ : 1;
         }
         int64_t grid = (int64_t)sm_count * g_occ_dec;
-        if (grid > L.max_tiles) grid = L.max_tiles;
+        if (grid > (L.max_tiles + dv.groups - 1) / dv.groups) grid = (L.max_tiles + dv.groups - 1) / dv.groups;
         if (grid < 1) grid = 1;
         dv.fn<<<(unsigned)grid, threads, dyn, stream>>>(
             d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),

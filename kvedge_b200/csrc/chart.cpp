@@ -143,7 +143,7 @@ struct Yaml {
         return true;
     }
     void skip_blank() {
-        while (cur < lines.size() && (blank(lines[cur]) || lines[cur].compare(0, 3, "---") == 0 && cur == 0)) ++cur;
+        while (cur < lines.size() && (blank(lines[cur]) || (lines[cur].compare(0, 3, "---") == 0 && cur == 0))) ++cur;
     }
     // strip a trailing comment (a '#' preceded by white space, outside quotes)
     static std::string strip_comment(const std::string &s) {
