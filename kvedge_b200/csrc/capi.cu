@@ -12,6 +12,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -67,8 +68,18 @@ int sm_count_of_current_device(int *out) {
 }
 
 // ------------------------------------------------------------------ host-buffer pipeline
-constexpr int kSlots = 4;
-constexpr int64_t kChunkBytesDefault = 32ll << 20;  // input bytes per pipeline chunk
+constexpr int kSlots = 8;       // slots that exist; n_slots() of them are used
+constexpr int64_t kChunkBytesDefault = 16ll << 20;  // input bytes per pipeline chunk
+
+int n_slots() {
+    static int v = 0;
+    if (v == 0) {  // KVEDGE_SLOTS: tuning knob for tools/
+        const char *e = getenv("KVEDGE_SLOTS");
+        v = e && atoi(e) > 0 ? atoi(e) : 4;
+        if (v > kSlots) v = kSlots;
+    }
+    return v;
+}
 
 int64_t chunk_bytes() {
     static int64_t v = 0;
@@ -79,10 +90,15 @@ int64_t chunk_bytes() {
     return v;
 }
 
+// A slot owns the device buffers of one chunk in flight.  Three streams carry the batch --
+// uploads, kernels, downloads -- and events chain a chunk through them, so the host submits the
+// whole batch without ever waiting for a download (waiting on per-slot "done" events let the
+// upload engine idle until the host woke up: measured 20.1 ms against a 17.3 ms copy-only floor).
 struct Slot {
-    cudaStream_t stream = nullptr;
-    cudaEvent_t done = nullptr;
-    bool busy = false;
+    cudaEvent_t up = nullptr;     // uploads of the chunk finished (host may rewrite h_ctl)
+    cudaEvent_t ran = nullptr;    // kernel finished
+    cudaEvent_t down = nullptr;   // downloads finished (device buffers free again)
+    bool used = false;
     char *d_in = nullptr;   size_t cap_in = 0;
     char *d_out = nullptr;  size_t cap_out = 0;
     // control block, same layout on both sides so that ONE copy ships it:
@@ -94,6 +110,7 @@ struct Slot {
 struct HostCtx {
     int device = 0;
     bool ready = false;
+    cudaStream_t s_up = nullptr, s_run = nullptr, s_down = nullptr;
     Slot slot[kSlots];
 };
 HostCtx g_ctx;
@@ -135,20 +152,48 @@ int ctx_init() {
     if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
     if (n <= 0) return fail(KV_ENODEVICE, "no CUDA device (this library has no CPU fallback)");
     KV_CUDA(cudaSetDevice(g_ctx.device));
+    KV_CUDA(cudaStreamCreateWithFlags(&g_ctx.s_up, cudaStreamNonBlocking));
+    KV_CUDA(cudaStreamCreateWithFlags(&g_ctx.s_run, cudaStreamNonBlocking));
+    KV_CUDA(cudaStreamCreateWithFlags(&g_ctx.s_down, cudaStreamNonBlocking));
     for (int i = 0; i < kSlots; ++i) {
-        KV_CUDA(cudaStreamCreateWithFlags(&g_ctx.slot[i].stream, cudaStreamNonBlocking));
-        KV_CUDA(cudaEventCreateWithFlags(&g_ctx.slot[i].done, cudaEventDisableTiming));
+        KV_CUDA(cudaEventCreateWithFlags(&g_ctx.slot[i].up, cudaEventDisableTiming));
+        KV_CUDA(cudaEventCreateWithFlags(&g_ctx.slot[i].ran, cudaEventDisableTiming));
+        KV_CUDA(cudaEventCreateWithFlags(&g_ctx.slot[i].down, cudaEventDisableTiming));
     }
     g_ctx.ready = true;
     return KV_OK;
 }
 
-int slot_wait(Slot &s) {
-    if (s.busy) {
-        KV_CUDA(cudaEventSynchronize(s.done));
-        s.busy = false;
+// KVEDGE_TRACE=1: per-chunk device timeline of a host batch on stderr (tools/ only).
+struct ChunkTrace { cudaEvent_t e[4]; double host[5]; };  // before H2D, after H2D, after kernel, after D2H; host clock at each mark
+std::vector<ChunkTrace> g_trace;
+bool trace_on() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("KVEDGE_TRACE"); v = e && atoi(e) > 0 ? 1 : 0; }
+    return v == 1;
+}
+void trace_mark(int which, cudaStream_t st) {
+    if (!trace_on()) return;
+    if (which == 0) {
+        ChunkTrace t;
+        for (auto &e : t.e) cudaEventCreate(&e);
+        g_trace.push_back(t);
     }
-    return KV_OK;
+    cudaEventRecord(g_trace.back().e[which], st);
+    g_trace.back().host[which] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+void trace_dump() {
+    if (!trace_on() || g_trace.empty()) return;
+    for (size_t i = 0; i < g_trace.size(); ++i) {
+        float t[4];
+        for (int k = 0; k < 4; ++k) cudaEventElapsedTime(&t[k], g_trace[0].e[0], g_trace[i].e[k]);
+        const double h0 = g_trace[0].host[0];
+        fprintf(stderr, "chunk %2zu: h2d %7.3f..%7.3f  kernel ..%7.3f  d2h ..%7.3f ms   host submits at %7.3f %7.3f %7.3f %7.3f\n", i,
+                t[0], t[1], t[2], t[3], g_trace[i].host[0] - h0, g_trace[i].host[1] - h0, g_trace[i].host[2] - h0, g_trace[i].host[3] - h0);
+    }
+    for (auto &c : g_trace)
+        for (auto &e : c.e) cudaEventDestroy(e);
+    g_trace.clear();
 }
 
 // Run units [lo, hi) of a host packed batch through one slot. mode 0 = encode, 1 = decode.
@@ -158,14 +203,20 @@ int slot_wait(Slot &s) {
 int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *out,
               const int64_t *out_off, int64_t lo, int64_t hi, int64_t *out_len,
               int64_t *status, int sm_count) {
-    int rc = slot_wait(s);
-    if (rc) return rc;
+    int rc;
+    // the previous chunk in this slot: its uploads must be over before h_ctl is rewritten
+    // (long past), and its downloads before the device buffers are written again (ordered on
+    // the device, not by the host)
+    if (s.used) KV_CUDA(cudaEventSynchronize(s.up));
     const int64_t n = hi - lo;
     const int64_t ibeg = in_off[lo], iend = in_off[hi];
     const int64_t obeg = out_off[lo], oend = out_off[hi];
     const int64_t in_bytes = iend - ibeg, out_bytes = oend - obeg;
     // keep each unit's alignment (mod 16) identical on the device and on the host side
-    const int64_t ishift = ibeg & 15, oshift = obeg & 15;
+    // and give the device side of each copy the host side's offset inside a 4 KiB page: the copy
+    // engines run measurably below their rate when source and destination are skewed
+    const int64_t ishift = (int64_t)(reinterpret_cast<uintptr_t>(in + ibeg) & 4095u);
+    const int64_t oshift = (int64_t)(reinterpret_cast<uintptr_t>(out + obeg) & 4095u);
     const int tile = mode == 0 ? kvedge::kEncTileIn : kvedge::dec_tile_in();
     const kvedge::ScratchLayout L = kvedge::scratch_layout(n, in_bytes + ishift, tile);
     const size_t off_in = 0, off_out = (size_t)(n + 1) * 8, off_len = off_out + (size_t)(n + 1) * 8;
@@ -187,33 +238,52 @@ int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *ou
     const int64_t n_tiles = kvedge::plan_tiles_host(h_in_off, h_out_off, n, tile, mode, L,
                                                     s.h_ctl + off_scratch, h_len, h_status);
     const size_t ctl_used = off_scratch + L.desc_off + (size_t)n_tiles * sizeof(kvedge::TileDesc);
-    KV_CUDA(cudaMemcpyAsync(s.d_ctl, s.h_ctl, ctl_used, cudaMemcpyHostToDevice, s.stream));
-    if (in_bytes > 0)
-        KV_CUDA(cudaMemcpyAsync(s.d_in + ishift, in + ibeg, (size_t)in_bytes, cudaMemcpyHostToDevice, s.stream));
+    cudaStream_t s_up = g_ctx.s_up, s_run = g_ctx.s_run, s_down = g_ctx.s_down;
+    if (s.used) KV_CUDA(cudaStreamWaitEvent(s_up, s.down, 0));
+    trace_mark(0, s_up);
+    KV_CUDA(cudaMemcpyAsync(s.d_ctl, s.h_ctl, ctl_used, cudaMemcpyHostToDevice, s_up));
+    if (in_bytes > 0) {
+        // An upload whose host address is not 256-byte aligned runs ~10 % slower and drags the
+        // concurrent download with it (tools/pcie_peak.py): send the ragged head on its own.
+        size_t head = (size_t)((256u - (reinterpret_cast<uintptr_t>(in + ibeg) & 255u)) & 255u);
+        if (head > (size_t)in_bytes) head = (size_t)in_bytes;
+        if (head) KV_CUDA(cudaMemcpyAsync(s.d_in + ishift, in + ibeg, head, cudaMemcpyHostToDevice, s_up));
+        if ((size_t)in_bytes > head)
+            KV_CUDA(cudaMemcpyAsync(s.d_in + ishift + head, in + ibeg + head, (size_t)in_bytes - head, cudaMemcpyHostToDevice, s_up));
+    }
+    trace_mark(1, s_up);
+    KV_CUDA(cudaEventRecord(s.up, s_up));
+    KV_CUDA(cudaStreamWaitEvent(s_run, s.up, 0));
     const int64_t *d_in_off = reinterpret_cast<const int64_t *>(s.d_ctl + off_in);
     const int64_t *d_out_off = reinterpret_cast<const int64_t *>(s.d_ctl + off_out);
     int64_t *d_len = reinterpret_cast<int64_t *>(s.d_ctl + off_len);
     int64_t *d_status = reinterpret_cast<int64_t *>(s.d_ctl + off_status);
     cudaError_t e = cudaSuccess;
-    if (n_tiles > 0) {
+    static int diag = -1;  // KVEDGE_E2E_DIAG (tools/ only): 1 = no kernel, 2 = also no upload->download ordering
+    if (diag < 0) { const char *d = getenv("KVEDGE_E2E_DIAG"); diag = d ? atoi(d) : 0; }
+    if (n_tiles > 0 && diag == 0) {
         if (mode == 0)
             e = kvedge::launch_b64enc_run(reinterpret_cast<const uint8_t *>(s.d_in), d_in_off, n,
                                           in_bytes + ishift, s.d_out, s.d_ctl + off_scratch, L.total,
-                                          s.stream, sm_count);
+                                          s_run, sm_count);
         else
             e = kvedge::launch_b64dec_run(s.d_in, d_in_off, n, in_bytes + ishift,
                                           reinterpret_cast<uint8_t *>(s.d_out), d_out_off, d_len, d_status,
-                                          s.d_ctl + off_scratch, L.total, s.stream, sm_count);
+                                          s.d_ctl + off_scratch, L.total, s_run, sm_count);
     }
     if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+    trace_mark(2, s_run);
+    KV_CUDA(cudaEventRecord(s.ran, s_run));
+    if (diag != 2) KV_CUDA(cudaStreamWaitEvent(s_down, s.ran, 0));
     if (out_bytes > 0)
-        KV_CUDA(cudaMemcpyAsync(out + obeg, s.d_out + oshift, (size_t)out_bytes, cudaMemcpyDeviceToHost, s.stream));
+        KV_CUDA(cudaMemcpyAsync(out + obeg, s.d_out + oshift, (size_t)out_bytes, cudaMemcpyDeviceToHost, s_down));
     if (mode == 1) {
-        KV_CUDA(cudaMemcpyAsync(out_len + lo, d_len, (size_t)n * 8, cudaMemcpyDeviceToHost, s.stream));
-        KV_CUDA(cudaMemcpyAsync(status + lo, d_status, (size_t)n * 8, cudaMemcpyDeviceToHost, s.stream));
+        KV_CUDA(cudaMemcpyAsync(out_len + lo, d_len, (size_t)n * 8, cudaMemcpyDeviceToHost, s_down));
+        KV_CUDA(cudaMemcpyAsync(status + lo, d_status, (size_t)n * 8, cudaMemcpyDeviceToHost, s_down));
     }
-    KV_CUDA(cudaEventRecord(s.done, s.stream));
-    s.busy = true;
+    trace_mark(3, s_down);
+    KV_CUDA(cudaEventRecord(s.down, s_down));
+    s.used = true;
     return KV_OK;
 }
 
@@ -244,16 +314,20 @@ int run_host_batch(int mode, const char *in, const int64_t *in_off, int64_t n_un
     while (lo < n_units) {
         int64_t hi = lo + 1;
         while (hi < n_units && in_off[hi + 1] - in_off[lo] <= chunk_bytes()) ++hi;
-        rc = run_chunk(g_ctx.slot[turn % kSlots], mode, in, in_off, out, out_off, lo, hi, out_len,
+        rc = run_chunk(g_ctx.slot[turn % n_slots()], mode, in, in_off, out, out_off, lo, hi, out_len,
                        status, sms);
         if (rc) break;
         lo = hi;
         ++turn;
     }
-    for (int i = 0; i < kSlots; ++i) {
-        int r2 = slot_wait(g_ctx.slot[i]);
-        if (!rc) rc = r2;
-    }
+    // everything a chunk does ends in the download stream
+    cudaError_t e1 = cudaStreamSynchronize(g_ctx.s_down);
+    cudaError_t e2 = cudaStreamSynchronize(g_ctx.s_run);
+    cudaError_t e3 = cudaStreamSynchronize(g_ctx.s_up);
+    if (!rc && e1 != cudaSuccess) rc = cuda_fail(e1, "download stream");
+    if (!rc && e2 != cudaSuccess) rc = cuda_fail(e2, "kernel stream");
+    if (!rc && e3 != cudaSuccess) rc = cuda_fail(e3, "upload stream");
+    trace_dump();
     return rc;
 }
 
@@ -408,17 +482,22 @@ void kv_shutdown(void) {
     std::lock_guard<std::mutex> lk(g_mu);
     if (!g_ctx.ready) return;
     cudaSetDevice(g_ctx.device);
+    cudaDeviceSynchronize();
     for (int i = 0; i < kSlots; ++i) {
         Slot &s = g_ctx.slot[i];
-        if (s.busy) cudaEventSynchronize(s.done);
         if (s.d_in) cudaFree(s.d_in);
         if (s.d_out) cudaFree(s.d_out);
         if (s.d_ctl) cudaFree(s.d_ctl);
         if (s.h_ctl) cudaFreeHost(s.h_ctl);
-        if (s.done) cudaEventDestroy(s.done);
-        if (s.stream) cudaStreamDestroy(s.stream);
+        if (s.up) cudaEventDestroy(s.up);
+        if (s.ran) cudaEventDestroy(s.ran);
+        if (s.down) cudaEventDestroy(s.down);
         s = Slot();
     }
+    if (g_ctx.s_up) cudaStreamDestroy(g_ctx.s_up);
+    if (g_ctx.s_run) cudaStreamDestroy(g_ctx.s_run);
+    if (g_ctx.s_down) cudaStreamDestroy(g_ctx.s_down);
+    g_ctx.s_up = g_ctx.s_run = g_ctx.s_down = nullptr;
     g_ctx.ready = false;
 }
 
