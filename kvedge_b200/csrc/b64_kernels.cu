@@ -113,13 +113,13 @@ plan_emit(const int64_t *__restrict__ in_off, const int64_t *__restrict__ out_of
         if (len < 0) len = 0;
         obeg = out_off[u];
         cnt = len > 0 ? (int)((len + tile_in - 1) / tile_in) : 0;
-        if (MODE == 1) {
+        if (MODE == 1 && blockIdx.y == 0) {
             out_len[u] = len / 4 * 3;
             status[u] = (len & 3) ? -2 : -1;  // -2: not canonical -> b64dec_slow decides
         }
     }
     int first = base_sh + block_excl_scan(cnt, &total);
-    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+    if (blockIdx.x == gridDim.x - 1 && blockIdx.y == 0 && threadIdx.x == 0) {
         // A caller that understated total_in_bytes sized the table too small: never write past
         // it (the batch then comes out truncated, and header[3] says so, but memory stays intact).
         header[0] = base_sh + total <= max_tiles ? base_sh + total : max_tiles;
@@ -127,17 +127,35 @@ plan_emit(const int64_t *__restrict__ in_off, const int64_t *__restrict__ out_of
         header[2] = 0;
         header[3] = base_sh + total > max_tiles ? 1 : 0;
     }
-    for (int k = 0; k < cnt; ++k) {
+    auto emit = [&](int64_t e_ibeg, int64_t e_obeg, int64_t e_len, int64_t e_u, int e_first, int e_cnt, int k) {
         int64_t s = (int64_t)k * tile_in;
         TileDesc d;
-        d.in_pos = ibeg + s;
-        d.out_pos = obeg + (MODE == 0 ? s / 3 * 4 : s / 4 * 3);
-        int64_t rem = len - s;
+        d.in_pos = e_ibeg + s;
+        d.out_pos = e_obeg + (MODE == 0 ? s / 3 * 4 : s / 4 * 3);
+        int64_t rem = e_len - s;
         d.len = (int32_t)(rem < tile_in ? rem : tile_in);
-        d.unit = (int32_t)u;
-        d.flags = (k == cnt - 1) ? 1 : 0;
+        d.unit = (int32_t)e_u;
+        d.flags = (k == e_cnt - 1) ? 1 : 0;
         d.pad = 0;
-        if (first + k < max_tiles) desc[first + k] = d;
+        if (e_first + k < max_tiles) desc[e_first + k] = d;
+    };
+    // A unit of one or two tiles is written by its own thread; a long unit (a 1 MiB Secret is
+    // 86 tiles) by its whole warp, or the plan would take longer than the encode.
+    // When the batch is a few very long units, gridDim.y blocks share each plan block's units
+    // (they all redo the scan, which is cheap) and split the long units' tiles between them.
+    constexpr int kOwn = 2;
+    if (cnt <= kOwn && blockIdx.y == 0)
+        for (int k = 0; k < cnt; ++k) emit(ibeg, obeg, len, u, first, cnt, k);
+    unsigned long_mask = __ballot_sync(0xffffffffu, cnt > kOwn);
+    const int lane = threadIdx.x & 31;
+    while (long_mask) {
+        const int src = __ffs(long_mask) - 1;
+        long_mask &= long_mask - 1;
+        const int64_t b_ibeg = __shfl_sync(0xffffffffu, ibeg, src), b_obeg = __shfl_sync(0xffffffffu, obeg, src);
+        const int64_t b_len = __shfl_sync(0xffffffffu, len, src), b_u = __shfl_sync(0xffffffffu, u, src);
+        const int b_first = __shfl_sync(0xffffffffu, first, src), b_cnt = __shfl_sync(0xffffffffu, cnt, src);
+        for (int k = lane + 32 * (int)blockIdx.y; k < b_cnt; k += 32 * (int)gridDim.y)
+            emit(b_ibeg, b_obeg, b_len, b_u, b_first, b_cnt, k);
     }
 }
 
@@ -898,10 +916,12 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
         }
     } else {
         // ------------------------------------------------------------------ consumers
-        const int cw = role - 1;
+        // Which warp takes a stage's first iteration rotates from stage to stage: a 2.4 KB tile is
+        // 6.3 warp-iterations, and with fixed roles the same warps would always carry the extra one.
+        int cw = role - 1;
         const EncMeta *gmeta = meta[grp];
         uint32_t s = 0, ph = 0;
-        for (;;) {
+        for (;; cw = cw + 1 == kConsumerWarps ? 0 : cw + 1) {
             mbar_wait_a(full_a + s * 8u, ph);
             const int4 hot = *reinterpret_cast<const int4 *>(&gmeta[s]);
             const int len = hot.z;
@@ -1282,13 +1302,15 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
         }
     } else {
         // ------------------------------------------------------------------ consumers
-        const int cw = role - 1;
+        // cw: this warp's turn inside the current stage; it rotates from stage to stage so that the
+        // warps carrying a short tile's extra iteration and its tail are not always the same ones
+        int cw = role - 1;
         const uint32_t lane4 = (uint32_t)lane * 4u;
         const uint32_t lut_lane = pinned_smem_u32(lut_words) + lane4;
         uint32_t *ow_buf = obuf[grp * kConsumerWarps + cw];
         const DecMeta *gmeta = meta[grp];
         uint32_t s = 0, ph = 0;
-        for (;;) {
+        for (;; cw = cw + 1 == kConsumerWarps ? 0 : cw + 1) {
             mbar_wait_a(full_a + s * 8u, ph);
             const int4 hot = *reinterpret_cast<const int4 *>(&gmeta[s]);
             const int len = hot.z;
@@ -1646,12 +1668,16 @@ static cudaError_t plan(const int64_t *d_in_off, const int64_t *d_out_off, int64
     TileDesc *desc = reinterpret_cast<TileDesc *>(base + L.desc_off);
     unsigned nb = (unsigned)L.n_plan_blocks;
     plan_count<<<nb, kPlanBlock, 0, stream>>>(d_in_off, n_units, tile_in, block_sums);
+    // more than ~2048 tiles per plan block on average: a few very long units; share them out
+    int64_t ny = L.max_tiles / ((int64_t)nb * 2048);
+    ny = ny < 1 ? 1 : (ny > 32 ? 32 : ny);
+    const dim3 grid(nb, (unsigned)ny);
     if (mode == 0)
-        plan_emit<0><<<nb, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in,
-                                                    block_sums, header, desc, (int)L.max_tiles, nullptr, nullptr);
+        plan_emit<0><<<grid, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in,
+                                                      block_sums, header, desc, (int)L.max_tiles, nullptr, nullptr);
     else
-        plan_emit<1><<<nb, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in,
-                                                    block_sums, header, desc, (int)L.max_tiles, d_out_len, d_status);
+        plan_emit<1><<<grid, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in,
+                                                      block_sums, header, desc, (int)L.max_tiles, d_out_len, d_status);
     return cudaGetLastError();
 }
 
