@@ -65,25 +65,68 @@ __device__ __forceinline__ int block_excl_scan(int v, int *total) {
     return incl - v + warp_sums[wid];
 }
 
+// Tiles come in two kinds.  A unit longer than small_max is cut into pieces of tile_in bytes,
+// one tile each ("solo" tiles).  Shorter units are not worth a pipeline stage of their own (a
+// stage costs the same bookkeeping whether it holds 300 bytes or 12 KiB), so a run of consecutive
+// short units whose first bytes fall into the same window of (tile_in - small_max) input bytes
+// becomes ONE "group" tile: its span is at most tile_in bytes, and the consumer warps take whole
+// units of it in turn.  A run also ends at a plan-block boundary, which keeps the rule local.
+// small_max == 0 turns grouping off (the older kernels only understand solo tiles).
+__host__ __device__ inline bool group_starts_at(const int64_t *in_off, int64_t u, int small_max, int window) {
+    if (u % kPlanBlock == 0) return true;
+    if (in_off[u] - in_off[u - 1] > small_max) return true;   // the unit before is a long one
+    return in_off[u] / window != in_off[u - 1] / window;
+}
+__host__ __device__ inline int unit_tile_count(const int64_t *in_off, int64_t u, int tile_in, int small_max) {
+    const int64_t len = in_off[u + 1] - in_off[u];
+    if (len <= small_max) return small_max > 0 && group_starts_at(in_off, u, small_max, tile_in - small_max) ? 1 : 0;
+    return (int)((len + tile_in - 1) / tile_in);
+}
+
 __global__ void __launch_bounds__(kPlanBlock)
-plan_count(const int64_t *__restrict__ in_off, int64_t n_units, int tile_in,
+plan_count(const int64_t *__restrict__ in_off, int64_t n_units, int tile_in, int small_max,
            int *__restrict__ block_sums) {
     __shared__ int total;
     int64_t u = (int64_t)blockIdx.x * kPlanBlock + threadIdx.x;
     int cnt = 0;
-    if (u < n_units) {
-        int64_t len = in_off[u + 1] - in_off[u];
-        cnt = len > 0 ? (int)((len + tile_in - 1) / tile_in) : 0;
-    }
+    if (u < n_units) cnt = unit_tile_count(in_off, u, tile_in, small_max);
     (void)block_excl_scan(cnt, &total);
     if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+// For every thread: the smallest value held by a thread with a HIGHER index in the block
+// (kPlanBlock for the last one).  v is the thread's own index if it is flagged, else kPlanBlock.
+__device__ __forceinline__ int block_next_flagged(int v) {
+    __shared__ int warp_min[32], warp_suffix[32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {   // inclusive suffix minimum inside the warp
+        int t = __shfl_down_sync(0xffffffffu, v, d);
+        if (lane + d < 32) v = min(v, t);
+    }
+    if (lane == 0) warp_min[wid] = v;
+    __syncthreads();
+    if (wid == 0) {
+        int x = warp_min[lane];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int t = __shfl_down_sync(0xffffffffu, x, d);
+            if (lane + d < 32) x = min(x, t);
+        }
+        int y = __shfl_down_sync(0xffffffffu, x, 1);
+        warp_suffix[lane] = lane == 31 ? kPlanBlock : y;   // exclusive: warps after this one
+    }
+    __syncthreads();
+    int nxt = __shfl_down_sync(0xffffffffu, v, 1);
+    if (lane == 31) nxt = kPlanBlock;
+    return min(nxt, warp_suffix[wid]);
 }
 
 // MODE 0: encode (out step 4 bytes per 3 in). MODE 1: decode (3 per 4) + status init.
 template <int MODE>
 __global__ void __launch_bounds__(kPlanBlock)
 plan_emit(const int64_t *__restrict__ in_off, const int64_t *__restrict__ out_off,
-          int64_t n_units, int tile_in, const int *__restrict__ block_sums,
+          int64_t n_units, int tile_in, int small_max, const int *__restrict__ block_sums,
           int *__restrict__ header, TileDesc *__restrict__ desc, int max_tiles,
           int64_t *__restrict__ out_len, int64_t *__restrict__ status) {
     __shared__ int total;
@@ -112,7 +155,7 @@ plan_emit(const int64_t *__restrict__ in_off, const int64_t *__restrict__ out_of
         len = in_off[u + 1] - ibeg;
         if (len < 0) len = 0;
         obeg = out_off[u];
-        cnt = len > 0 ? (int)((len + tile_in - 1) / tile_in) : 0;
+        cnt = unit_tile_count(in_off, u, tile_in, small_max);
         if (MODE == 1 && blockIdx.y == 0) {
             out_len[u] = len / 4 * 3;
             status[u] = (len & 3) ? -2 : -1;  // -2: not canonical -> b64dec_slow decides
@@ -126,7 +169,36 @@ plan_emit(const int64_t *__restrict__ in_off, const int64_t *__restrict__ out_of
         header[1] = 0;  // tile counter and finished-block counter of the consuming kernel
         header[2] = 0;
         header[3] = base_sh + total > max_tiles ? 1 : 0;
+        // group tiles carry no output position: the kernels look each unit's up here
+        const unsigned long long op = (unsigned long long)reinterpret_cast<uintptr_t>(out_off);
+        header[4] = (int)(unsigned)(op & 0xffffffffull);
+        header[5] = (int)(unsigned)(op >> 32);
     }
+    // a group runs from its first unit to the next flagged one (a long unit or another group's start)
+    const bool is_small = u < n_units && len <= small_max;
+    const bool flagged = u < n_units ? (!is_small || cnt > 0) : true;
+    const int next_flagged = block_next_flagged(flagged ? (int)threadIdx.x : kPlanBlock);
+    if (is_small && cnt > 0 && blockIdx.y == 0) {
+        int64_t last = (int64_t)blockIdx.x * kPlanBlock + next_flagged;
+        if (last > n_units) last = n_units;
+        TileDesc d;
+        d.in_pos = ibeg;
+        d.unit = (int32_t)u;
+        if (last - u == 1) {
+            // alone between two long units: an ordinary tile, shared by all consumer warps
+            d.out_pos = obeg;
+            d.len = (int32_t)len;
+            d.flags = 1;
+            d.pad = 0;
+        } else {
+            d.out_pos = 0;
+            d.len = (int32_t)(in_off[last] - ibeg);
+            d.flags = 2;                  // bit1: group tile; pad = number of units in it
+            d.pad = (int32_t)(last - u);
+        }
+        if (first < max_tiles) desc[first] = d;
+    }
+    if (is_small) cnt = 0;   // nothing more to emit for it below
     auto emit = [&](int64_t e_ibeg, int64_t e_obeg, int64_t e_len, int64_t e_u, int e_first, int e_cnt, int k) {
         int64_t s = (int64_t)k * tile_in;
         TileDesc d;
@@ -761,13 +833,14 @@ b64enc_stream(const uint8_t *__restrict__ in, char *__restrict__ out,
 // What the encode producer tells its consumers about a stage; the first 16 bytes are all the
 // hot path reads.
 struct __align__(16) EncMeta {
-    char *dst;           // where this stage's characters go
+    char *dst;           // where this stage's characters go (solo tiles)
     int len;             // input bytes in this stage; < 0: no more work
     uint32_t info;       // bits 0-3: offset of the first input byte in its 16-byte chunk; bit 8:
                          // destination 16-byte aligned; bit 9: byte-wise stage (no bulk copy);
-                         // bits 16..: byte offset of the stage inside the group's ring
-    const uint8_t *src;  // byte-wise stages only
-    int64_t pad;
+                         // bit 10: group tile; bits 16..: byte offset of the stage inside the ring
+    int64_t in_pos;      // where the stage's first byte sits in the input blob
+    int unit;            // group tile: first unit and how many
+    int count;
 };
 
 __device__ __forceinline__ uint32_t pinned_u32(uint32_t a) {
@@ -840,10 +913,15 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
                 const int64_t out_pos = ((int64_t)(uint32_t)__shfl_sync(0xffffffffu, d0.w, t) << 32) |
                                         (uint32_t)__shfl_sync(0xffffffffu, d0.z, t);
                 const int len = __shfl_sync(0xffffffffu, d1.x, t);
+                const int unit = __shfl_sync(0xffffffffu, d1.y, t);
+                const int tflags = __shfl_sync(0xffffffffu, d1.z, t);
+                const int ucount = __shfl_sync(0xffffffffu, d1.w, t);
                 if (lane != 0) continue;
+                if (len <= 0 || len > kStageIn) continue;   // a group of empty units; or offsets that are not sorted
+                const bool is_group = (tflags & 2) != 0;
                 const uint8_t *src = in + in_pos;
                 char *dst = out + out_pos;
-                const uint32_t dalign = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
+                const uint32_t dalign = is_group ? 0u : (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
                 // the bulk copy fetches whole 16-byte lines around the tile: keep it inside the blob
                 const bool bulk_ok = in_pos >= 16 && in_pos + len + 16 <= in_end && (dalign & 3u) == 0;
                 const uint32_t s = c % kStages;
@@ -877,9 +955,11 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
                 EncMeta m;
                 m.dst = dst;
                 m.len = len;
-                m.info = sh | (dalign == 0 ? 0x100u : 0u) | (bulk_ok ? 0u : 0x200u) | (boff << 12);  // boff % 16 == 0
-                m.src = src;
-                m.pad = 0;
+                m.info = sh | (dalign == 0 ? 0x100u : 0u) | (bulk_ok ? 0u : 0x200u) | (is_group ? 0x400u : 0u) |
+                         (boff << 12);  // boff % 16 == 0
+                m.in_pos = in_pos;
+                m.unit = unit;
+                m.count = ucount;
                 meta[grp][s] = m;
                 if (bulk_ok) {
                     const uint32_t bytes = (sh + (uint32_t)len + 15u) & ~15u;
@@ -916,12 +996,12 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
         }
     } else {
         // ------------------------------------------------------------------ consumers
-        // Which warp takes a stage's first iteration rotates from stage to stage: a 2.4 KB tile is
-        // 6.3 warp-iterations, and with fixed roles the same warps would always carry the extra one.
-        int cw = role - 1;
+        const int cw = role - 1;
         const EncMeta *gmeta = meta[grp];
+        const int64_t *out_off = reinterpret_cast<const int64_t *>(
+            ((unsigned long long)(unsigned)header[5] << 32) | (unsigned long long)(unsigned)header[4]);
         uint32_t s = 0, ph = 0;
-        for (;; cw = cw + 1 == kConsumerWarps ? 0 : cw + 1) {
+        for (;;) {
             mbar_wait_a(full_a + s * 8u, ph);
             const int4 hot = *reinterpret_cast<const int4 *>(&gmeta[s]);
             const int len = hot.z;
@@ -929,8 +1009,46 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
             const uint32_t info = (uint32_t)hot.w, sh = info & 15u;
             const uint8_t *buf = ring + (info >> 12);
             char *dst = reinterpret_cast<char *>(((uint64_t)(uint32_t)hot.y << 32) | (uint32_t)hot.x);
-            if (info & 0x200u) {
-                const uint8_t *src = gmeta[s].src;
+            if (info & 0x400u) {
+                // group tile: whole short units, one warp each in turn
+                const int u0 = gmeta[s].unit, cnt = gmeta[s].count;
+                const int64_t tpos = gmeta[s].in_pos;
+                // offsets of 32 units at a time, one per lane: one round trip to L2 per 32 units
+                // instead of three dependent ones per unit
+                for (int base = 0; base < cnt; base += 32) {
+                int64_t la = 0, lb = 0, lo = 0;
+                if (base + lane < cnt) {
+                    la = in_off[u0 + base + lane];
+                    lb = in_off[u0 + base + lane + 1];
+                    lo = out_off[u0 + base + lane];
+                }
+                const int hi = cnt - base < 32 ? cnt - base : 32;
+                for (int k = (cw + kConsumerWarps - base % kConsumerWarps) % kConsumerWarps; k < hi; k += kConsumerWarps) {
+                    const int64_t a = __shfl_sync(0xffffffffu, la, k);
+                    const int ulen = (int)(__shfl_sync(0xffffffffu, lb, k) - a);
+                    const int64_t uo = __shfl_sync(0xffffffffu, lo, k);
+                    if (ulen <= 0) continue;
+                    char *udst = out + uo;
+                    const uint32_t ual = (uint32_t)(reinterpret_cast<uintptr_t>(udst) & 15u);
+                    if ((info & 0x200u) || (ual & 3u)) {   // not staged, or a destination words cannot reach
+                        for (int off = lane * 12; off < ulen; off += 384)
+                            encode_bytes(in + a + off, udst + off / 3 * 4, (ulen - off) < 12 ? (ulen - off) : 12);
+                        continue;
+                    }
+                    const uint32_t bo = sh + (uint32_t)(a - tpos);
+                    const uint8_t *ubuf = buf + (bo & ~15u);
+                    const uint32_t ush = bo & 15u;
+                    if (ual == 0) {
+                        if (ush & 3u) encode_stage<true, true, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
+                        else encode_stage<true, false, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
+                    } else {
+                        if (ush & 3u) encode_stage<false, true, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
+                        else encode_stage<false, false, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
+                    }
+                }
+                }
+            } else if (info & 0x200u) {
+                const uint8_t *src = in + gmeta[s].in_pos;
                 for (int off = cw * 384 + lane * 12; off < len; off += 384 * kConsumerWarps)
                     encode_bytes(src + off, dst + off / 3 * 4, (len - off) < 12 ? (len - off) : 12);
             } else if (info & 0x100u) {
@@ -1068,10 +1186,11 @@ struct __align__(16) DecMeta {
     uint8_t *dst;        // where this stage's bytes go
     int len;             // characters in this stage; < 0: no more work
     uint32_t info;       // bits 0-3: offset of the first character in the stage buffer;
-                         // bit 8: last tile of its unit; bit 9: byte-wise stage (no bulk copy)
+                         // bit 8: last tile of its unit; bit 9: byte-wise stage (no bulk copy);
+                         // bit 10: group tile; bits 16..: byte offset of the stage inside the ring
     const uint8_t *src;  // global address of the first character (byte-wise stages, out_len)
-    int unit;
-    int pad;
+    int unit;            // the unit (solo tile) or the first unit (group tile) ...
+    int count;           // ... and how many units a group tile holds
 };
 
 // A shared address the compiler cannot rematerialise (it would otherwise rebuild the
@@ -1151,6 +1270,114 @@ __device__ __forceinline__ void decode_tail(const uint8_t *buf, uint32_t sh, uin
     __syncwarp();
 }
 
+// The general path: byte-wise stages, destinations that are not 16-byte aligned, and any
+// piece whose end needs care.  Warp-iterations ow0, ow0 + kStep, ... of a piece of `len`
+// characters that starts `sh` bytes into `buf` (staged pieces) or at `src` in global memory
+// (byte-wise ones).  The lane that meets the end of the unit stores its decoded length.
+template <int kStep>
+__device__ __forceinline__ void decode_general(const uint8_t *buf, uint32_t sh, const uint8_t *src, uint8_t *dst,
+                                               int ow0, int len, bool last_tile, bool bytewise,
+                                               const uint32_t *lut_words, int lane, uint32_t *bad_v, uint32_t *bad_w,
+                                               int64_t *out_len_slot, int64_t chars_before) {
+    const uint32_t lane4 = (uint32_t)lane * 4u;
+    const uint32_t sh4 = sh & 3u, s8 = sh4 * 8;
+    for (int ow = ow0; ow < len; ow += kStep) {   // warp-uniform loop
+        const int off = ow + lane * 16;
+        const bool active = off < len;
+        const int nvalid = !active ? 0 : ((len - off) < 16 ? (len - off) : 16);  // a multiple of 4
+        uint32_t w[4] = {0x41414141u, 0x41414141u, 0x41414141u, 0x41414141u};
+        if (!bytewise && active) {
+            // 16-byte loads (a lane-per-chunk LDS.128 is bank-conflict free; four LDS.32
+            // at a 16-byte lane stride would be 4-way conflicted), then a uniform word
+            // select and byte funnel for pieces that do not start on a 16-byte boundary
+            const uint4 *vp = reinterpret_cast<const uint4 *>(buf + off);
+            const uint4 A = vp[0];
+            w[0] = A.x; w[1] = A.y; w[2] = A.z; w[3] = A.w;
+            if (sh) {
+                const uint4 B = vp[1];
+                uint32_t w4 = B.x;
+                const uint32_t ws = sh >> 2;
+                if (ws == 1) { w[0] = A.y; w[1] = A.z; w[2] = A.w; w[3] = B.x; w4 = B.y; }
+                else if (ws == 2) { w[0] = A.z; w[1] = A.w; w[2] = B.x; w[3] = B.y; w4 = B.z; }
+                else if (ws == 3) { w[0] = A.w; w[1] = B.x; w[2] = B.y; w[3] = B.z; w4 = B.w; }
+                if (sh4) {
+                    w[0] = __funnelshift_r(w[0], w[1], s8);
+                    w[1] = __funnelshift_r(w[1], w[2], s8);
+                    w[2] = __funnelshift_r(w[2], w[3], s8);
+                    w[3] = __funnelshift_r(w[3], w4, s8);
+                }
+            }
+            if (nvalid < 16) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g)
+                    if (g * 4 >= nvalid) w[g] = 0x41414141u;
+            }
+        } else if (active) {
+            const uint8_t *p = src + off;
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                if (i < nvalid) {
+                    const uint32_t mk = 0xFFu << (8 * (i & 3));
+                    w[i >> 2] = (w[i >> 2] & ~mk) | ((uint32_t)p[i] << (8 * (i & 3)));
+                }
+        }
+        int npad = 0;
+        const int nq = nvalid >> 2;
+        if (active && last_tile && off + nvalid == len) {
+            // '=' padding is legal only in the last quantum of the unit
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+                if (g == nq - 1 && (w[g] >> 24) == 0x3Du) {
+                    npad = 1;
+                    w[g] = (w[g] & 0x00FFFFFFu) | 0x41000000u;
+                    if (((w[g] >> 16) & 0xFFu) == 0x3Du) {
+                        npad = 2;
+                        w[g] = (w[g] & 0xFF00FFFFu) | 0x00410000u;
+                    }
+                }
+            *out_len_slot = (chars_before + off + nvalid) / 4 * 3 - npad;
+        }
+        const uint32_t n0 = decode_word_char(w[0], lut_words, lane4, bad_v, bad_w);
+        const uint32_t n1 = decode_word_char(w[1], lut_words, lane4, bad_v, bad_w);
+        const uint32_t n2 = decode_word_char(w[2], lut_words, lane4, bad_v, bad_w);
+        const uint32_t n3 = decode_word_char(w[3], lut_words, lane4, bad_v, bad_w);
+        // 4 x 24 bits (big-endian inside each group) -> 12 bytes in stream order
+        const uint32_t o0 = __byte_perm(n0, n1, 0x6012);
+        const uint32_t o1 = __byte_perm(n1, n2, 0x5601);
+        const uint32_t o2 = __byte_perm(n2, n3, 0x4560);
+        uint8_t *q = dst + off / 4 * 3;
+        const int nbytes = nq * 3 - npad;
+        if (!bytewise && nbytes == 12) {
+            uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
+            q4[0] = o0; q4[1] = o1; q4[2] = o2;
+        } else if (active) {
+            const uint32_t o[3] = {o0, o1, o2};
+#pragma unroll
+            for (int i = 0; i < 12; ++i)
+                if (i < nbytes) q[i] = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
+        }
+    }
+}
+
+// decode_plain for a stage offset known only at run time: eight instantiations, one jump.
+template <int kConsumerWarps>
+__device__ __forceinline__ void decode_plain_any(uint32_t sh, const uint8_t *buf, uint32_t lut_lane, uint32_t *ow_buf,
+                                                 uint8_t *dst, int ow0, int plain_end, int lane,
+                                                 uint32_t *bad_v, uint32_t *bad_w) {
+    const uint32_t ws = sh >> 2, s8 = (sh & 3u) * 8;
+    if ((sh & 3u) == 0) {
+        if (ws == 0) decode_plain<0, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, bad_v, bad_w);
+        else if (ws == 1) decode_plain<1, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, bad_v, bad_w);
+        else if (ws == 2) decode_plain<2, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, bad_v, bad_w);
+        else decode_plain<3, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, bad_v, bad_w);
+    } else {
+        if (ws == 0) decode_plain<0, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, bad_v, bad_w);
+        else if (ws == 1) decode_plain<1, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, bad_v, bad_w);
+        else if (ws == 2) decode_plain<2, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, bad_v, bad_w);
+        else decode_plain<3, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, bad_v, bad_w);
+    }
+}
+
 // One block per SM holds kGroups independent pipelines -- each a producer warp, its own ring
 // of kStages tiles and kConsumerWarps consumer warps -- around ONE character table.
 // Dynamic shared memory: [table, kDecLutBytes][kGroups rings of kStages * stride bytes].
@@ -1225,11 +1452,14 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                 const int len = __shfl_sync(0xffffffffu, d1.x, t);
                 const int unit = __shfl_sync(0xffffffffu, d1.y, t);
                 const int tflags = __shfl_sync(0xffffffffu, d1.z, t);
+                const int ucount = __shfl_sync(0xffffffffu, d1.w, t);
                 if (lane != 0) continue;
-                if (len & 3) continue;  // unit length not a multiple of 4: flagged by the plan (-2)
+                const bool is_group = (tflags & 2) != 0;
+                if (!is_group && (len & 3)) continue;  // unit length not a multiple of 4: flagged by the plan (-2)
+                if (len <= 0 || len > kTile) continue;  // a group of empty units; or offsets that are not sorted
                 const uint8_t *src = reinterpret_cast<const uint8_t *>(in) + in_pos;
                 uint8_t *dst = out + out_pos;
-                const bool dst4 = (reinterpret_cast<uintptr_t>(dst) & 3u) == 0;
+                const bool dst4 = is_group || (reinterpret_cast<uintptr_t>(dst) & 3u) == 0;
                 const bool bulk_ok = in_pos >= 16 && in_pos + len + 16 <= in_end && dst4;
                 const uint32_t s = c % kStages;
                 const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
@@ -1263,10 +1493,11 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                 DecMeta m;
                 m.dst = dst;
                 m.len = len;
-                m.info = sh | ((uint32_t)(tflags & 1) << 8) | (bulk_ok ? 0u : 0x200u) | (boff << 12);  // boff is a multiple of 16
+                m.info = sh | ((uint32_t)(tflags & 1) << 8) | (bulk_ok ? 0u : 0x200u) | (is_group ? 0x400u : 0u) |
+                         (boff << 12);  // boff is a multiple of 16
                 m.src = src;
                 m.unit = unit;
-                m.pad = 0;
+                m.count = ucount;
                 meta[grp][s] = m;
                 if (bulk_ok) {
                     const uint32_t bytes = (sh + (uint32_t)len + 15u) & ~15u;
@@ -1302,15 +1533,15 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
         }
     } else {
         // ------------------------------------------------------------------ consumers
-        // cw: this warp's turn inside the current stage; it rotates from stage to stage so that the
-        // warps carrying a short tile's extra iteration and its tail are not always the same ones
-        int cw = role - 1;
+        const int cw = role - 1;
         const uint32_t lane4 = (uint32_t)lane * 4u;
         const uint32_t lut_lane = pinned_smem_u32(lut_words) + lane4;
         uint32_t *ow_buf = obuf[grp * kConsumerWarps + cw];
         const DecMeta *gmeta = meta[grp];
+        const int64_t *out_off = reinterpret_cast<const int64_t *>(
+            ((unsigned long long)(unsigned)header[5] << 32) | (unsigned long long)(unsigned)header[4]);
         uint32_t s = 0, ph = 0;
-        for (;; cw = cw + 1 == kConsumerWarps ? 0 : cw + 1) {
+        for (;;) {
             mbar_wait_a(full_a + s * 8u, ph);
             const int4 hot = *reinterpret_cast<const int4 *>(&gmeta[s]);
             const int len = hot.z;
@@ -1319,120 +1550,68 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
             const bool last_tile = (info & 0x100u) != 0, bytewise = (info & 0x200u) != 0;
             const uint8_t *buf = ring + ((info >> 12) & ~15u);
             uint8_t *dst = reinterpret_cast<uint8_t *>(((uint64_t)(uint32_t)hot.y << 32) | (uint32_t)hot.x);
-            const uint32_t sh4 = sh & 3u, s8 = sh4 * 8;
-            uint32_t bad_v = 0, bad_w = 0;
-            const bool dst16 = (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
-            // Plain iterations (all 32 lanes full, the unit cannot end inside) go through the
-            // branch-free templated loop; the stage's last warp-iteration takes decode_tail;
-            // byte-wise stages and unaligned destinations take the general code below.
-            int ow0 = cw * 512;
-            if (!bytewise && dst16) {
-                const int plain_len = last_tile ? len - 1 : len;          // iterations with ow + 512 <= plain_len
-                const int n_it = plain_len >= ow0 + 512 ? (int)((uint32_t)(plain_len - ow0 - 512) / (512u * kConsumerWarps)) + 1 : 0;
-                const int plain_end = ow0 + n_it * 512 * kConsumerWarps;  // first ow not handled here
-                if (n_it > 0) {
-                    const uint32_t ws = sh >> 2;
-                    if (sh4 == 0) {
-                        if (ws == 0) decode_plain<0, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
-                        else if (ws == 1) decode_plain<1, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
-                        else if (ws == 2) decode_plain<2, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
-                        else decode_plain<3, false, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+            if (info & 0x400u) {
+                // group tile: whole short units, one warp each in turn
+                const int u0 = gmeta[s].unit, cnt = gmeta[s].count;
+                const uint8_t *tsrc = gmeta[s].src;
+                const int64_t tpos = tsrc - reinterpret_cast<const uint8_t *>(in);
+                for (int j = cw; j < cnt; j += kConsumerWarps) {
+                    const int u = u0 + j;
+                    const int64_t a = in_off[u];
+                    const int ulen = (int)(in_off[u + 1] - a);
+                    if (ulen <= 0 || (ulen & 3)) continue;   // empty, or already flagged by the plan
+                    uint8_t *udst = out + out_off[u];
+                    const uint32_t bo = sh + (uint32_t)(a - tpos);
+                    const uint8_t *ubuf = buf + (bo & ~15u);
+                    const uint32_t ush = bo & 15u;
+                    const uint32_t ual = (uint32_t)(reinterpret_cast<uintptr_t>(udst) & 15u);
+                    uint32_t bv = 0, bw = 0;
+                    if (!bytewise && ual == 0) {
+                        const int plain_end = (ulen - 1) / 512 * 512;   // iterations that cannot hold the end
+                        if (plain_end > 0) decode_plain_any<1>(ush, ubuf, lut_lane, ow_buf, udst, 0, plain_end, lane, &bv, &bw);
+                        int npad = 0;
+                        decode_tail(ubuf, ush, lut_lane, ow_buf, udst, plain_end, ulen, true, lane, &bv, &bw, &npad);
+                        if (lane == 0) out_len[u] = (int64_t)(ulen / 4 * 3 - npad);
                     } else {
-                        if (ws == 0) decode_plain<0, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
-                        else if (ws == 1) decode_plain<1, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
-                        else if (ws == 2) decode_plain<2, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
-                        else decode_plain<3, true, kConsumerWarps>(buf, lut_lane, ow_buf, dst, ow0, plain_end, s8, lane, &bad_v, &bad_w);
+                        decode_general<512>(ubuf, ush, tsrc + (a - tpos), udst, 0, ulen, true, bytewise || (ual & 3u) != 0,
+                                            lut_words, lane, &bv, &bw, &out_len[u], 0);
                     }
-                    ow0 = plain_end;
+                    if ((bv & kDecBadMask) || (bw & 0x80808080u)) status[u] = -2;
                 }
-                if (ow0 < len) {   // this warp owns the stage's last warp-iteration
-                    int npad = 0;
-                    decode_tail(buf, sh, lut_lane, ow_buf, dst, ow0, len, last_tile, lane, &bad_v, &bad_w, &npad);
-                    if (last_tile && lane == 0) {
-                        const int unit = gmeta[s].unit;
-                        out_len[unit] = (int64_t)(gmeta[s].src - reinterpret_cast<const uint8_t *>(in) - in_off[unit] + len) / 4 * 3 - npad;
+            } else {
+                uint32_t bad_v = 0, bad_w = 0;
+                const bool dst16 = (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
+                // Plain iterations (all 32 lanes full, the unit cannot end inside) go through the
+                // branch-free templated loop; the stage's last warp-iteration takes decode_tail;
+                // byte-wise stages and unaligned destinations take the general code.
+                int ow0 = cw * 512;
+                if (!bytewise && dst16) {
+                    const int plain_len = last_tile ? len - 1 : len;          // iterations with ow + 512 <= plain_len
+                    const int n_it = plain_len >= ow0 + 512 ? (int)((uint32_t)(plain_len - ow0 - 512) / (512u * kConsumerWarps)) + 1 : 0;
+                    const int plain_end = ow0 + n_it * 512 * kConsumerWarps;  // first ow not handled here
+                    if (n_it > 0) {
+                        decode_plain_any<kConsumerWarps>(sh, buf, lut_lane, ow_buf, dst, ow0, plain_end, lane, &bad_v, &bad_w);
+                        ow0 = plain_end;
                     }
-                    ow0 = len;
+                    if (ow0 < len) {   // this warp owns the stage's last warp-iteration
+                        int npad = 0;
+                        decode_tail(buf, sh, lut_lane, ow_buf, dst, ow0, len, last_tile, lane, &bad_v, &bad_w, &npad);
+                        if (last_tile && lane == 0) {
+                            const int unit = gmeta[s].unit;
+                            out_len[unit] = (int64_t)(gmeta[s].src - reinterpret_cast<const uint8_t *>(in) - in_off[unit] + len) / 4 * 3 - npad;
+                        }
+                        ow0 = len;
+                    }
                 }
-            }
-            for (int ow = ow0; ow < len; ow += 512 * kConsumerWarps) {   // warp-uniform loop
-                const int off = ow + lane * 16;
-                const bool active = off < len;
-                const int nvalid = !active ? 0 : ((len - off) < 16 ? (len - off) : 16);  // a multiple of 4
-                uint32_t w[4] = {0x41414141u, 0x41414141u, 0x41414141u, 0x41414141u};
-                if (!bytewise && active) {
-                    // 16-byte loads (a lane-per-chunk LDS.128 is bank-conflict free; four LDS.32
-                    // at a 16-byte lane stride would be 4-way conflicted), then a uniform word
-                    // select and byte funnel for stages that do not start on a 16-byte boundary
-                    const uint4 *vp = reinterpret_cast<const uint4 *>(buf + off);
-                    const uint4 A = vp[0];
-                    w[0] = A.x; w[1] = A.y; w[2] = A.z; w[3] = A.w;
-                    if (sh) {
-                        const uint4 B = vp[1];
-                        uint32_t w4 = B.x;
-                        const uint32_t ws = sh >> 2;
-                        if (ws == 1) { w[0] = A.y; w[1] = A.z; w[2] = A.w; w[3] = B.x; w4 = B.y; }
-                        else if (ws == 2) { w[0] = A.z; w[1] = A.w; w[2] = B.x; w[3] = B.y; w4 = B.z; }
-                        else if (ws == 3) { w[0] = A.w; w[1] = B.x; w[2] = B.y; w[3] = B.z; w4 = B.w; }
-                        if (sh4) {
-                            w[0] = __funnelshift_r(w[0], w[1], s8);
-                            w[1] = __funnelshift_r(w[1], w[2], s8);
-                            w[2] = __funnelshift_r(w[2], w[3], s8);
-                            w[3] = __funnelshift_r(w[3], w4, s8);
-                        }
-                    }
-                    if (nvalid < 16) {
-#pragma unroll
-                        for (int g = 0; g < 4; ++g)
-                            if (g * 4 >= nvalid) w[g] = 0x41414141u;
-                    }
-                } else if (active) {
-                    const uint8_t *p = gmeta[s].src + off;
-#pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (i < nvalid) {
-                            const uint32_t mk = 0xFFu << (8 * (i & 3));
-                            w[i >> 2] = (w[i >> 2] & ~mk) | ((uint32_t)p[i] << (8 * (i & 3)));
-                        }
-                }
-                int npad = 0;
-                const int nq = nvalid >> 2;
-                if (active && last_tile && off + nvalid == len) {
-                    // '=' padding is legal only in the last quantum of the unit
-#pragma unroll
-                    for (int g = 0; g < 4; ++g)
-                        if (g == nq - 1 && (w[g] >> 24) == 0x3Du) {
-                            npad = 1;
-                            w[g] = (w[g] & 0x00FFFFFFu) | 0x41000000u;
-                            if (((w[g] >> 16) & 0xFFu) == 0x3Du) {
-                                npad = 2;
-                                w[g] = (w[g] & 0xFF00FFFFu) | 0x00410000u;
-                            }
-                        }
+                if (ow0 < len) {
                     const int unit = gmeta[s].unit;
-                    out_len[unit] = (int64_t)(gmeta[s].src - reinterpret_cast<const uint8_t *>(in) - in_off[unit] + off + nvalid) / 4 * 3 - npad;
+                    const uint8_t *src = gmeta[s].src;
+                    decode_general<512 * kConsumerWarps>(buf, sh, src, dst, ow0, len, last_tile, bytewise, lut_words, lane,
+                                                         &bad_v, &bad_w, &out_len[unit],
+                                                         (int64_t)(src - reinterpret_cast<const uint8_t *>(in)) - in_off[unit]);
                 }
-                const uint32_t n0 = decode_word_char(w[0], lut_words, lane4, &bad_v, &bad_w);
-                const uint32_t n1 = decode_word_char(w[1], lut_words, lane4, &bad_v, &bad_w);
-                const uint32_t n2 = decode_word_char(w[2], lut_words, lane4, &bad_v, &bad_w);
-                const uint32_t n3 = decode_word_char(w[3], lut_words, lane4, &bad_v, &bad_w);
-                // 4 x 24 bits (big-endian inside each group) -> 12 bytes in stream order
-                const uint32_t o0 = __byte_perm(n0, n1, 0x6012);
-                const uint32_t o1 = __byte_perm(n1, n2, 0x5601);
-                const uint32_t o2 = __byte_perm(n2, n3, 0x4560);
-                uint8_t *q = dst + off / 4 * 3;
-                const int nbytes = nq * 3 - npad;
-                if (!bytewise && nbytes == 12) {
-                    uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
-                    q4[0] = o0; q4[1] = o1; q4[2] = o2;
-                } else if (active) {
-                    const uint32_t o[3] = {o0, o1, o2};
-#pragma unroll
-                    for (int i = 0; i < 12; ++i)
-                        if (i < nbytes) q[i] = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
-                }
+                if ((bad_v & kDecBadMask) || (bad_w & 0x80808080u)) status[gmeta[s].unit] = -2;  // benign race: every writer stores the same value
             }
-            if ((bad_v & kDecBadMask) || (bad_w & 0x80808080u)) status[gmeta[s].unit] = -2;  // benign race: every writer stores the same value
             __syncwarp();
             if (lane == 0) mbar_arrive_a(empty_a + s * 8u);
             if (++s == kStages) { s = 0; ph ^= 1u; }
@@ -1624,8 +1803,8 @@ __global__ void b64dec_slow(const char *__restrict__ in, const int64_t *__restri
 // points know every offset already, so they write the table into pinned memory and ship it
 // with the offsets in one copy instead of launching two planning kernels per chunk.
 int64_t plan_tiles_host(const int64_t *in_off, const int64_t *out_off, int64_t n_units, int tile_in,
-                        int mode, const ScratchLayout &L, void *scratch_host, int64_t *out_len,
-                        int64_t *status) {
+                        int small_max, int mode, const ScratchLayout &L, void *scratch_host,
+                        const int64_t *d_out_off, int64_t *out_len, int64_t *status) {
     char *base = static_cast<char *>(scratch_host);
     int *header = reinterpret_cast<int *>(base);
     TileDesc *desc = reinterpret_cast<TileDesc *>(base + L.desc_off);
@@ -1637,6 +1816,30 @@ int64_t plan_tiles_host(const int64_t *in_off, const int64_t *out_off, int64_t n
         if (mode == 1) {
             out_len[u] = len / 4 * 3;
             status[u] = (len & 3) ? -2 : -1;
+        }
+        if (len <= small_max) {   // same rule as plan_count / plan_emit
+            if (small_max > 0 && group_starts_at(in_off, u, small_max, tile_in - small_max)) {
+                int64_t last = u + 1;
+                while (last < n_units && in_off[last + 1] - in_off[last] <= small_max &&
+                       !group_starts_at(in_off, last, small_max, tile_in - small_max))
+                    ++last;
+                TileDesc d;
+                d.in_pos = ibeg;
+                d.unit = (int32_t)u;
+                if (last - u == 1) {
+                    d.out_pos = out_off[u];
+                    d.len = (int32_t)len;
+                    d.flags = 1;
+                    d.pad = 0;
+                } else {
+                    d.out_pos = 0;
+                    d.len = (int32_t)(in_off[last] - ibeg);
+                    d.flags = 2;
+                    d.pad = (int32_t)(last - u);
+                }
+                desc[t++] = d;
+            }
+            continue;
         }
         for (int64_t s = 0; s < len; s += tile_in, ++t) {
             TileDesc d;
@@ -1653,6 +1856,10 @@ int64_t plan_tiles_host(const int64_t *in_off, const int64_t *out_off, int64_t n
     header[0] = (int)t;
     header[1] = 0;
     header[2] = 0;
+    header[3] = 0;
+    const unsigned long long op = (unsigned long long)reinterpret_cast<uintptr_t>(d_out_off);
+    header[4] = (int)(unsigned)(op & 0xffffffffull);
+    header[5] = (int)(unsigned)(op >> 32);
     return t;
 }
 
@@ -1660,26 +1867,40 @@ int64_t plan_tiles_host(const int64_t *in_off, const int64_t *out_off, int64_t n
 static int g_occ_enc = 0, g_occ_dec = 0;
 
 static cudaError_t plan(const int64_t *d_in_off, const int64_t *d_out_off, int64_t n_units,
-                        int tile_in, int mode, const ScratchLayout &L, void *d_scratch,
+                        int tile_in, int small_max, int mode, const ScratchLayout &L, void *d_scratch,
                         int64_t *d_out_len, int64_t *d_status, cudaStream_t stream) {
     char *base = static_cast<char *>(d_scratch);
     int *header = reinterpret_cast<int *>(base);
     int *block_sums = reinterpret_cast<int *>(base + L.block_sums_off);
     TileDesc *desc = reinterpret_cast<TileDesc *>(base + L.desc_off);
     unsigned nb = (unsigned)L.n_plan_blocks;
-    plan_count<<<nb, kPlanBlock, 0, stream>>>(d_in_off, n_units, tile_in, block_sums);
+    plan_count<<<nb, kPlanBlock, 0, stream>>>(d_in_off, n_units, tile_in, small_max, block_sums);
     // more than ~2048 tiles per plan block on average: a few very long units; share them out
     int64_t ny = L.max_tiles / ((int64_t)nb * 2048);
     ny = ny < 1 ? 1 : (ny > 32 ? 32 : ny);
     const dim3 grid(nb, (unsigned)ny);
     if (mode == 0)
-        plan_emit<0><<<grid, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in,
+        plan_emit<0><<<grid, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in, small_max,
                                                       block_sums, header, desc, (int)L.max_tiles, nullptr, nullptr);
     else
-        plan_emit<1><<<grid, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in,
+        plan_emit<1><<<grid, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in, small_max,
                                                       block_sums, header, desc, (int)L.max_tiles, d_out_len, d_status);
     return cudaGetLastError();
 }
+
+// Which encode kernel a batch gets: the KVEDGE_ENC_VARIANT knob (tools/), and for the default
+// the grouped kernel (200) unless the batch is tiny.  The plan and the run must agree on it,
+// because only the grouped kernels understand group tiles.
+static int enc_variant_for(const ScratchLayout &L) {
+    static int latched = -1;
+    if (latched < 0) {
+        const char *v = getenv("KVEDGE_ENC_VARIANT");
+        latched = v ? atoi(v) : 0;
+        if (latched < 0) latched = 0;
+    }
+    return latched == 0 && L.max_tiles > 32 ? 200 : latched;
+}
+int enc_small_max(const ScratchLayout &L) { return enc_variant_for(L) >= 200 ? kEncTileIn / 4 : 0; }
 
 cudaError_t launch_b64enc_plan(const int64_t *d_in_off, int64_t n_units, int64_t total_in_bytes,
                                const int64_t *d_out_off, void *d_scratch, size_t scratch_bytes,
@@ -1687,7 +1908,7 @@ cudaError_t launch_b64enc_plan(const int64_t *d_in_off, int64_t n_units, int64_t
     if (n_units <= 0) return cudaSuccess;
     ScratchLayout L = scratch_layout(n_units, total_in_bytes, kEncTileIn);
     if (scratch_bytes < L.total) return cudaErrorInvalidValue;
-    return plan(d_in_off, d_out_off, n_units, kEncTileIn, 0, L, d_scratch, nullptr, nullptr, stream);
+    return plan(d_in_off, d_out_off, n_units, kEncTileIn, enc_small_max(L), 0, L, d_scratch, nullptr, nullptr, stream);
 }
 
 cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
@@ -1702,18 +1923,11 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
                                           b64enc_tiles<8, false, 0>, b64enc_tiles<8, true, 1>,
                                           b64enc_tiles<8, true, 3>, b64enc_tiles<6, true, 2>,
                                           b64enc_tiles<8, true, -1>, b64enc_tiles<8, true, -2>};
-    static int variant_latched = -1;
-    if (variant_latched < 0) {  // tuning knob for tools/; the default is variant 0
-        const char *v = getenv("KVEDGE_ENC_VARIANT");
-        variant_latched = v ? atoi(v) : 0;
-        if (variant_latched < 0) variant_latched = 0;
-    }
-    int variant = variant_latched;
-    cudaError_t e;
     // The product kernel is the grouped one (200); a tiny batch (a single render) takes the
     // one-pipeline, all-arithmetic build below, which has no table to fill.  KVEDGE_ENC_VARIANT=1..
     // selects the one-pipeline-per-block kernels, 100.. the load/store kernels, 201.. other group shapes.
-    if (variant == 0 && L.max_tiles > 32) variant = 200;
+    int variant = enc_variant_for(L);
+    cudaError_t e;
     if (variant >= 200) {  // grouped pipelines: several producer/consumer groups per block around one table
         struct GroupVariant { EncKernel fn; int groups, stages, consumers, ring, lut; };
         static const GroupVariant kGroup[] = {
@@ -1856,6 +2070,7 @@ static int dec_variant() {
 }
 
 int dec_tile_in() { return dec_variant() < 100 ? kDec[dec_variant()].tile : kDecTileIn; }
+int dec_small_max() { return dec_variant() < 100 ? dec_tile_in() / 4 : 0; }
 
 cudaError_t launch_b64dec(const char *d_in, const int64_t *d_in_off, int64_t n_units,
                           int64_t total_in_bytes, uint8_t *d_out, const int64_t *d_out_off,
@@ -1864,7 +2079,7 @@ cudaError_t launch_b64dec(const char *d_in, const int64_t *d_in_off, int64_t n_u
     if (n_units <= 0) return cudaSuccess;
     ScratchLayout L = scratch_layout(n_units, total_in_bytes, dec_tile_in());
     if (scratch_bytes < L.total) return cudaErrorInvalidValue;
-    cudaError_t e = plan(d_in_off, d_out_off, n_units, dec_tile_in(), 1, L, d_scratch, d_out_len,
+    cudaError_t e = plan(d_in_off, d_out_off, n_units, dec_tile_in(), dec_small_max(), 1, L, d_scratch, d_out_len,
                          d_status, stream);
     if (e != cudaSuccess) return e;
     return launch_b64dec_run(d_in, d_in_off, n_units, total_in_bytes, d_out, d_out_off, d_out_len,

@@ -16,6 +16,7 @@ constexpr int kEncTileOut = kEncTileIn / 3 * 4;
 constexpr int kDecTileIn = 16384;
 constexpr int kMinTileIn = 8192;  // sizes the scratch
 int dec_tile_in();
+int dec_small_max();   // units up to this many characters are grouped into shared tiles (0: never)
 constexpr int kThreads = 256;
 constexpr int kPlanBlock = 1024;  // units per block in the plan kernels
 
@@ -25,8 +26,8 @@ struct __align__(32) TileDesc {
     int64_t out_pos;  // absolute byte offset in the output blob
     int32_t len;      // input bytes in this tile (<= tile size)
     int32_t unit;     // unit index
-    int32_t flags;    // bit0: last tile of its unit
-    int32_t pad;
+    int32_t flags;    // bit0: last tile of its unit; bit1: group tile (see plan_count)
+    int32_t pad;      // group tile: number of consecutive units, starting at `unit`, it holds
 };
 
 // Scratch layout (device memory owned by the caller of the *_dev entry points):
@@ -68,8 +69,11 @@ cudaError_t launch_b64dec_run(const char *d_in, const int64_t *d_in_off, int64_t
 // Host-side twin of the plan kernels: writes header + TileDesc table into `scratch_host`
 // (a host mirror of the scratch, laid out by L) and, for decode (mode 1), the initial
 // out_len / status values.  Returns the number of tiles.
+// small_max: enc_small_max(L) / dec_small_max().  d_out_off: where out_off will live on the
+// device (group tiles make the kernels read it).
 int64_t plan_tiles_host(const int64_t *in_off, const int64_t *out_off, int64_t n_units, int tile_in,
-                        int mode, const ScratchLayout &L, void *scratch_host, int64_t *out_len,
-                        int64_t *status);
+                        int small_max, int mode, const ScratchLayout &L, void *scratch_host,
+                        const int64_t *d_out_off, int64_t *out_len, int64_t *status);
+int enc_small_max(const ScratchLayout &L);
 
 }  // namespace kvedge

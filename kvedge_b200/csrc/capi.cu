@@ -235,8 +235,11 @@ int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *ou
         h_in_off[k] = in_off[lo + k] - ibeg + ishift;
         h_out_off[k] = out_off[lo + k] - obeg + oshift;
     }
-    const int64_t n_tiles = kvedge::plan_tiles_host(h_in_off, h_out_off, n, tile, mode, L,
-                                                    s.h_ctl + off_scratch, h_len, h_status);
+    const int small_max = mode == 0 ? kvedge::enc_small_max(L) : kvedge::dec_small_max();
+    const int64_t n_tiles = kvedge::plan_tiles_host(h_in_off, h_out_off, n, tile, small_max, mode, L,
+                                                    s.h_ctl + off_scratch,
+                                                    reinterpret_cast<const int64_t *>(s.d_ctl + off_out),
+                                                    h_len, h_status);
     const size_t ctl_used = off_scratch + L.desc_off + (size_t)n_tiles * sizeof(kvedge::TileDesc);
     cudaStream_t s_up = g_ctx.s_up, s_run = g_ctx.s_run, s_down = g_ctx.s_down;
     if (s.used) KV_CUDA(cudaStreamWaitEvent(s_up, s.down, 0));

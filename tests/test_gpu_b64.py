@@ -236,3 +236,67 @@ def test_second_device_when_present(torch_cuda):
             got = d_dec.cpu().numpy().tobytes()
             for i, u in enumerate(units):
                 assert got[int(doff[i]):int(doff[i]) + len(u)] == u
+
+
+def _short_and_long_units(rng, n):
+    """Runs of short units (what the plan packs into group tiles), single short units between
+    long ones, empties, and sizes either side of the short/long limit."""
+    sizes = []
+    while len(sizes) < n:
+        kind = int(rng.integers(0, 6))
+        if kind == 0:
+            sizes += [int(x) for x in rng.integers(0, 40, int(rng.integers(1, 60)))]        # a run of tiny ones
+        elif kind == 1:
+            sizes += [int(x) for x in rng.integers(200, 3200, int(rng.integers(1, 12)))]    # a run of short ones
+        elif kind == 2:
+            sizes += [int(rng.integers(3073, 40000))]                                      # a long one
+        elif kind == 3:
+            sizes += [int(rng.choice([3071, 3072, 3073, 4095, 4096, 4097, 12287, 12288, 12289]))]
+        elif kind == 4:
+            sizes += [int(rng.integers(3073, 20000)), int(rng.integers(1, 3000)), int(rng.integers(3073, 20000))]
+        else:
+            sizes += [0] * int(rng.integers(1, 5))
+    return sizes[:n]
+
+
+@pytest.mark.parametrize("out_align,in_shift", [(16, 0), (4, 3), (1, 1)])
+def test_group_tiles_encode(torch_cuda, out_align, in_shift):
+    rng = np.random.default_rng(2024 + out_align)
+    units = [rng.bytes(s) for s in _short_and_long_units(rng, 3000)]
+    outs, raw, out_off = _dev_encode(torch_cuda, units, out_align=out_align, in_shift=in_shift)
+    for i, u in enumerate(units):
+        assert outs[i] == ob64.encode(u), (i, len(u))
+    # nothing outside the units' own output ranges was written
+    mask = np.ones(len(raw), dtype=bool)
+    for i, u in enumerate(units):
+        mask[int(out_off[i]):int(out_off[i]) + b64.encoded_len(len(u))] = False
+    assert (np.frombuffer(raw, dtype=np.uint8)[mask] == 0x7E).all()
+
+
+@pytest.mark.parametrize("align", [16, 1])
+def test_group_tiles_decode_clean_and_corrupt(torch_cuda, align):
+    rng = np.random.default_rng(77 + align)
+    units = []
+    for i, s in enumerate(_short_and_long_units(rng, 3000)):
+        enc = bytearray(ob64.encode(rng.bytes(s)))
+        kind = i % 7
+        if kind == 1 and len(enc) > 8:
+            enc[int(rng.integers(0, len(enc) - 4))] = ord("*")
+        elif kind == 2 and len(enc) > 8:
+            p = int(rng.integers(1, len(enc)))
+            enc[p:p] = b"\r\n"
+        elif kind == 3 and len(enc) > 8:
+            del enc[-1]
+        elif kind == 4 and len(enc) > 8:
+            enc[int(rng.integers(0, len(enc)))] = 0xC3
+        units.append(bytes(enc))
+    blob, off = workload.pack(units)
+    dec_off = b64.decode_offsets(off, align=align)
+    out, _, out_len, status = b64.b64dec_packed(blob, off, dec_off)
+    ref_out, ref_len, ref_status = ob64.decode_batch(blob, off, dec_off)
+    assert np.array_equal(status, ref_status)
+    assert np.array_equal(out_len, ref_len)
+    for i in range(len(units)):
+        a = out[int(dec_off[i]):int(dec_off[i]) + int(out_len[i])]
+        b = ref_out[int(dec_off[i]):int(dec_off[i]) + int(ref_len[i])]
+        assert np.array_equal(a, b), i
