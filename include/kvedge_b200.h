@@ -70,7 +70,9 @@ int kv_b64enc_batch_dev(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_
 
 /* The same call split in two, for callers that re-encode new bytes under unchanged offsets
  * (same fleet, new configs): kv_b64enc_plan_dev builds the tile table in d_scratch from the
- * offsets, kv_b64enc_run_dev runs the encode kernel over it.  plan + run == batch_dev.   */
+ * offsets, kv_b64enc_run_dev runs the encode kernel over it.  plan + run == batch_dev.
+ * The table remembers d_out_off (short units share tiles and look their output position up
+ * there), so both offset arrays must stay where they are, unchanged, while a plan is reused. */
 int kv_b64enc_plan_dev(const int64_t *d_in_off, int64_t n_units, int64_t total_in_bytes,
                        const int64_t *d_out_off, void *d_scratch, size_t scratch_bytes,
                        void *stream);
