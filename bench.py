@@ -243,6 +243,17 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     from kvedge_b200 import _lib
     _lib.check(_lib.lib().kv_set_device(local_rank))
+    # Several ranks on one host: keep each rank's threads and its pinned buffers on the GPU's own
+    # NUMA node, or every copy of the e2e leg crosses the socket interconnect.  Undone before the
+    # CPU baseline, which is meant to use every host core.
+    all_cpus = os.sched_getaffinity(0)
+    if world > 1:
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local_rank))
+        except Exception as e:  # noqa: BLE001  affinity is an optimisation, never a requirement
+            print(f"rank {rank}: no NUMA binding ({e})", file=sys.stderr)
 
     # ---- inputs: this rank's shard of the fleet (weak scaling: fixed installs per GPU)
     blob, in_off = build_fleet(args.installs, seed=rank)
@@ -405,6 +416,7 @@ def main():
             traffic = None
 
     threads = os.cpu_count() or 1
+    os.sched_setaffinity(0, all_cpus)
     cpu_rate, cpu_dt, cpu_passes, cpu_units = cpu_encode_rate(blob, in_off, threads, args.cpu_seconds, max_units=32768)
     cpu1_rate, _, _, _ = cpu_encode_rate(blob, in_off, 1, min(4.0, args.cpu_seconds), max_units=8192)
 
