@@ -37,6 +37,32 @@ ScratchLayout scratch_layout(int64_t n_units, int64_t total_in_bytes, int tile_i
     return L;
 }
 
+// ----------------------------------------------------------------------------- programmatic launch
+// plan_count -> plan_emit -> encode/decode kernel are launched back to back in one stream.  With
+// the programmatic-serialization launch attribute a kernel may start while its predecessor is
+// still running: pdl_launch_dependents() in the predecessor says "the next kernel may be
+// scheduled now", pdl_wait() in the successor blocks until the predecessor has completed and its
+// writes are visible.  Everything a kernel does before pdl_wait() (table fills, barrier
+// initialisation) therefore overlaps the predecessor, and the launch latency disappears.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_after_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                       Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 // ----------------------------------------------------------------------------- plan
 __device__ __forceinline__ int warp_incl_scan(int v) {
 #pragma unroll
@@ -87,6 +113,7 @@ __global__ void __launch_bounds__(kPlanBlock)
 plan_count(const int64_t *__restrict__ in_off, int64_t n_units, int tile_in, int small_max,
            int *__restrict__ block_sums) {
     __shared__ int total;
+    pdl_launch_dependents();   // plan_emit may be scheduled; it waits for our block_sums itself
     int64_t u = (int64_t)blockIdx.x * kPlanBlock + threadIdx.x;
     int cnt = 0;
     if (u < n_units) cnt = unit_tile_count(in_off, u, tile_in, small_max);
@@ -132,6 +159,8 @@ plan_emit(const int64_t *__restrict__ in_off, const int64_t *__restrict__ out_of
     __shared__ int total;
     __shared__ int base_sh;
     __shared__ int red[32];
+    pdl_launch_dependents();   // the encode/decode kernel may start its prologue
+    pdl_wait();                // plan_count's block_sums
     // tiles emitted by all earlier plan blocks
     int part = 0;
     for (int b = threadIdx.x; b < (int)blockIdx.x; b += kPlanBlock) part += block_sums[b];
@@ -882,6 +911,7 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    pdl_wait();   // everything above overlapped the plan; the tile table is read from here on
     const uint32_t full_a = pinned_u32(smem_u32(&full_bar[grp][0])), empty_a = pinned_u32(smem_u32(&empty_bar[grp][0]));
 
     if (role == 0) {
@@ -1419,6 +1449,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    pdl_wait();   // everything above overlapped the plan; the tile table is read from here on
     const uint32_t full_a = pinned_smem_u32(&full_bar[grp][0]), empty_a = pinned_smem_u32(&empty_bar[grp][0]);
 
     if (role == 0) {
@@ -1880,12 +1911,11 @@ static cudaError_t plan(const int64_t *d_in_off, const int64_t *d_out_off, int64
     ny = ny < 1 ? 1 : (ny > 32 ? 32 : ny);
     const dim3 grid(nb, (unsigned)ny);
     if (mode == 0)
-        plan_emit<0><<<grid, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in, small_max,
-                                                      block_sums, header, desc, (int)L.max_tiles, nullptr, nullptr);
-    else
-        plan_emit<1><<<grid, kPlanBlock, 0, stream>>>(d_in_off, d_out_off, n_units, tile_in, small_max,
-                                                      block_sums, header, desc, (int)L.max_tiles, d_out_len, d_status);
-    return cudaGetLastError();
+        return launch_after_kernel(plan_emit<0>, grid, dim3(kPlanBlock), 0, stream, d_in_off, d_out_off, n_units, tile_in,
+                                   small_max, (const int *)block_sums, header, desc, (int)L.max_tiles,
+                                   (int64_t *)nullptr, (int64_t *)nullptr);
+    return launch_after_kernel(plan_emit<1>, grid, dim3(kPlanBlock), 0, stream, d_in_off, d_out_off, n_units, tile_in,
+                               small_max, (const int *)block_sums, header, desc, (int)L.max_tiles, d_out_len, d_status);
 }
 
 // Which encode kernel a batch gets: the KVEDGE_ENC_VARIANT knob (tools/), and for the default
@@ -1965,10 +1995,9 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
         if (grid > (L.max_tiles + gv.groups - 1) / gv.groups) grid = (L.max_tiles + gv.groups - 1) / gv.groups;
         if (grid < 1) grid = 1;
         char *base = static_cast<char *>(d_scratch);
-        gv.fn<<<(unsigned)grid, threads, dyn, stream>>>(
-            d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
-            reinterpret_cast<int *>(base), d_in_off, n_units);
-        return cudaGetLastError();
+        return launch_after_kernel(gv.fn, dim3((unsigned)grid), dim3(threads), dyn, stream, d_in, d_out,
+                                   reinterpret_cast<const TileDesc *>(base + L.desc_off), reinterpret_cast<int *>(base),
+                                   d_in_off, n_units);
     }
     if (variant < 100) {  // streamed (bulk-copy ring) kernels; variant 0 is the product kernel
         struct StreamVariant { EncKernel fn; int stages, consumers, ring; };
@@ -2121,9 +2150,10 @@ cudaError_t launch_b64dec_run(const char *d_in, const int64_t *d_in_off, int64_t
         int64_t grid = (int64_t)sm_count * g_occ_dec;
         if (grid > (L.max_tiles + dv.groups - 1) / dv.groups) grid = (L.max_tiles + dv.groups - 1) / dv.groups;
         if (grid < 1) grid = 1;
-        dv.fn<<<(unsigned)grid, threads, dyn, stream>>>(
-            d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
-            reinterpret_cast<int *>(base), d_in_off, n_units, d_out_len, d_status);
+        e = launch_after_kernel(dv.fn, dim3((unsigned)grid), dim3(threads), dyn, stream, d_in, d_out,
+                                reinterpret_cast<const TileDesc *>(base + L.desc_off), reinterpret_cast<int *>(base),
+                                d_in_off, n_units, d_out_len, d_status);
+        if (e != cudaSuccess) return e;
     } else {
         if (g_occ_dec == 0) {
             int occ = 0;
