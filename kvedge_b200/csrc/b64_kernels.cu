@@ -1057,7 +1057,7 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
                     const int64_t a = __shfl_sync(0xffffffffu, la, k);
                     const int ulen = (int)(__shfl_sync(0xffffffffu, lb, k) - a);
                     const int64_t uo = __shfl_sync(0xffffffffu, lo, k);
-                    if (ulen <= 0) continue;
+                    if (ulen <= 0 || a < tpos || a + ulen > tpos + len) continue;   // empty; or offsets that are not sorted
                     char *udst = out + uo;
                     const uint32_t ual = (uint32_t)(reinterpret_cast<uintptr_t>(udst) & 15u);
                     if ((info & 0x200u) || (ual & 3u)) {   // not staged, or a destination words cannot reach
@@ -1591,6 +1591,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                     const int64_t a = in_off[u];
                     const int ulen = (int)(in_off[u + 1] - a);
                     if (ulen <= 0 || (ulen & 3)) continue;   // empty, or already flagged by the plan
+                    if (a < tpos || a + ulen > tpos + len) continue;   // offsets that are not sorted
                     uint8_t *udst = out + out_off[u];
                     const uint32_t bo = sh + (uint32_t)(a - tpos);
                     const uint8_t *ubuf = buf + (bo & ~15u);
