@@ -878,6 +878,49 @@ __device__ __forceinline__ uint32_t pinned_u32(uint32_t a) {
     return r;
 }
 
+// A group tile: whole short units, one consumer warp each in turn.  Out of line: the long-unit
+// path of the kernel keeps the registers and the code layout it had before group tiles existed.
+template <int kConsumerWarps, int NLUT>
+__device__ __noinline__ void encode_group_tile(const uint8_t *__restrict__ in, const int64_t *__restrict__ in_off,
+                                               char *__restrict__ out, const int64_t *__restrict__ out_off,
+                                               const uint8_t *buf, uint32_t sh, bool staged, int64_t tpos,
+                                               int u0, int cnt, int len, int cw, int lane, const uint16_t *lut) {
+    // offsets of 32 units at a time, one per lane: one round trip to L2 per 32 units instead of
+    // three dependent ones per unit
+    for (int base = 0; base < cnt; base += 32) {
+        int64_t la = 0, lb = 0, lo = 0;
+        if (base + lane < cnt) {
+            la = in_off[u0 + base + lane];
+            lb = in_off[u0 + base + lane + 1];
+            lo = out_off[u0 + base + lane];
+        }
+        const int hi = cnt - base < 32 ? cnt - base : 32;
+        for (int k = (cw + kConsumerWarps - base % kConsumerWarps) % kConsumerWarps; k < hi; k += kConsumerWarps) {
+            const int64_t a = __shfl_sync(0xffffffffu, la, k);
+            const int ulen = (int)(__shfl_sync(0xffffffffu, lb, k) - a);
+            const int64_t uo = __shfl_sync(0xffffffffu, lo, k);
+            if (ulen <= 0 || a < tpos || a + ulen > tpos + len) continue;   // empty; or offsets that are not sorted
+            char *udst = out + uo;
+            const uint32_t ual = (uint32_t)(reinterpret_cast<uintptr_t>(udst) & 15u);
+            if (!staged || (ual & 3u)) {   // not staged, or a destination words cannot reach
+                for (int off = lane * 12; off < ulen; off += 384)
+                    encode_bytes(in + a + off, udst + off / 3 * 4, (ulen - off) < 12 ? (ulen - off) : 12);
+                continue;
+            }
+            const uint32_t bo = sh + (uint32_t)(a - tpos);
+            const uint8_t *ubuf = buf + (bo & ~15u);
+            const uint32_t ush = bo & 15u;
+            if (ual == 0) {
+                if (ush & 3u) encode_stage<true, true, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
+                else encode_stage<true, false, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
+            } else {
+                if (ush & 3u) encode_stage<false, true, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
+                else encode_stage<false, false, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
+            }
+        }
+    }
+}
+
 // One block per SM (or two) holding kGroups independent pipelines -- a producer warp, a ring
 // and kConsumerWarps consumer warps each -- around ONE pair table.  Compared with
 // b64enc_stream (one pipeline per block) a 2.4 KB tile occupies four consumer warps instead
@@ -1040,43 +1083,8 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
             const uint8_t *buf = ring + (info >> 12);
             char *dst = reinterpret_cast<char *>(((uint64_t)(uint32_t)hot.y << 32) | (uint32_t)hot.x);
             if (info & 0x400u) {
-                // group tile: whole short units, one warp each in turn
-                const int u0 = gmeta[s].unit, cnt = gmeta[s].count;
-                const int64_t tpos = gmeta[s].in_pos;
-                // offsets of 32 units at a time, one per lane: one round trip to L2 per 32 units
-                // instead of three dependent ones per unit
-                for (int base = 0; base < cnt; base += 32) {
-                int64_t la = 0, lb = 0, lo = 0;
-                if (base + lane < cnt) {
-                    la = in_off[u0 + base + lane];
-                    lb = in_off[u0 + base + lane + 1];
-                    lo = out_off[u0 + base + lane];
-                }
-                const int hi = cnt - base < 32 ? cnt - base : 32;
-                for (int k = (cw + kConsumerWarps - base % kConsumerWarps) % kConsumerWarps; k < hi; k += kConsumerWarps) {
-                    const int64_t a = __shfl_sync(0xffffffffu, la, k);
-                    const int ulen = (int)(__shfl_sync(0xffffffffu, lb, k) - a);
-                    const int64_t uo = __shfl_sync(0xffffffffu, lo, k);
-                    if (ulen <= 0 || a < tpos || a + ulen > tpos + len) continue;   // empty; or offsets that are not sorted
-                    char *udst = out + uo;
-                    const uint32_t ual = (uint32_t)(reinterpret_cast<uintptr_t>(udst) & 15u);
-                    if ((info & 0x200u) || (ual & 3u)) {   // not staged, or a destination words cannot reach
-                        for (int off = lane * 12; off < ulen; off += 384)
-                            encode_bytes(in + a + off, udst + off / 3 * 4, (ulen - off) < 12 ? (ulen - off) : 12);
-                        continue;
-                    }
-                    const uint32_t bo = sh + (uint32_t)(a - tpos);
-                    const uint8_t *ubuf = buf + (bo & ~15u);
-                    const uint32_t ush = bo & 15u;
-                    if (ual == 0) {
-                        if (ush & 3u) encode_stage<true, true, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
-                        else encode_stage<true, false, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
-                    } else {
-                        if (ush & 3u) encode_stage<false, true, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
-                        else encode_stage<false, false, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
-                    }
-                }
-                }
+                encode_group_tile<kConsumerWarps, NLUT>(in, in_off, out, out_off, buf, sh, (info & 0x200u) == 0, gmeta[s].in_pos,
+                                                        gmeta[s].unit, gmeta[s].count, len, cw, lane, lut);
             } else if (info & 0x200u) {
                 const uint8_t *src = in + gmeta[s].in_pos;
                 for (int off = cw * 384 + lane * 12; off < len; off += 384 * kConsumerWarps)
