@@ -338,6 +338,23 @@ int run_host_batch(int mode, const char *in, const int64_t *in_off, int64_t n_un
 
 extern "C" {
 
+// Pinned staging for kv_fleet_template (render_capi.cpp): the fleet's packed inputs and their
+// encodings, kept between calls -- fresh pageable buffers of this size cost more in page faults
+// and staged copies than the encode itself.  Not part of the public header.
+static char *g_stage_in = nullptr, *g_stage_out = nullptr;
+static size_t g_stage_in_cap = 0, g_stage_out_cap = 0;
+int kv_stage_get_(size_t in_bytes, size_t out_bytes, char **in, char **out) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    int rc = ctx_init();
+    if (rc) return rc;
+    KV_CUDA(cudaSetDevice(g_ctx.device));
+    if ((rc = grow_pinned(&g_stage_in, &g_stage_in_cap, in_bytes + 256))) return rc;
+    if ((rc = grow_pinned(&g_stage_out, &g_stage_out_cap, out_bytes + 256))) return rc;
+    *in = g_stage_in;
+    *out = g_stage_out;
+    return KV_OK;
+}
+
 // shared with render_capi.cpp (not part of the public header)
 int kv_set_last_error_(int code, const char *msg) {
     g_err = msg ? msg : "";
@@ -497,6 +514,10 @@ void kv_shutdown(void) {
         if (s.down) cudaEventDestroy(s.down);
         s = Slot();
     }
+    if (g_stage_in) cudaFreeHost(g_stage_in);
+    if (g_stage_out) cudaFreeHost(g_stage_out);
+    g_stage_in = g_stage_out = nullptr;
+    g_stage_in_cap = g_stage_out_cap = 0;
     if (g_ctx.s_up) cudaStreamDestroy(g_ctx.s_up);
     if (g_ctx.s_run) cudaStreamDestroy(g_ctx.s_run);
     if (g_ctx.s_down) cudaStreamDestroy(g_ctx.s_down);

@@ -14,6 +14,7 @@
 #include <map>
 #include <memory>
 #include <atomic>
+#include <chrono>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -29,6 +30,7 @@ using kvedge::tmpl::TemplateSet;
 using kvedge::tmpl::Value;
 
 extern "C" int kv_set_last_error_(int code, const char *msg);  // capi.cu
+extern "C" int kv_stage_get_(size_t in_bytes, size_t out_bytes, char **in, char **out);  // capi.cu
 
 struct kv_chart {
     Chart chart;
@@ -204,6 +206,45 @@ void splice(std::string &text, const std::vector<Pending> &pending, const std::v
     }
 }
 
+// The same over a raw buffer, the encodings coming from one packed blob: site k's text is
+// enc[enc_off[k] .. + encoded_len).
+void splice_raw(char *text, size_t n, const std::vector<Pending> &pending, const char *enc, const int64_t *enc_off) {
+    for (size_t i = 0; i + 4 <= n;) {
+        unsigned char c = (unsigned char)text[i];
+        if (c >= 0x10 && c < 0x20) {
+            size_t id = 0;
+            for (int k = 0; k < 4; ++k) id = (id << 4) | ((unsigned char)text[i + (size_t)k] & 0xF);
+            if (id < pending.size() && i + pending[id].encoded_len <= n) {
+                memcpy(text + i, enc + enc_off[id], pending[id].encoded_len);
+                i += pending[id].encoded_len;
+                continue;
+            }
+        }
+        ++i;
+    }
+}
+
+// Run fn(i) for i in [0, n) on all host threads.
+template <typename F>
+void parallel_for(int n, F fn) {
+    unsigned n_thr = std::thread::hardware_concurrency();
+    if (n_thr == 0) n_thr = 1;
+    if (n_thr > 64) n_thr = 64;
+    if ((int)n_thr > n) n_thr = (unsigned)(n > 0 ? n : 1);
+    std::atomic<int> next{0};
+    auto work = [&]() {
+        for (;;) {
+            const int b = next.fetch_add(16);
+            if (b >= n) return;
+            for (int i = b; i < n && i < b + 16; ++i) fn(i);
+        }
+    };
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < n_thr; ++t) pool.emplace_back(work);
+    work();
+    for (auto &t : pool) t.join();
+}
+
 int plan_release(const kv_chart *c, const char *release, const char *ns, const kv_overrides *ov, bool defer,
                  kv_release **out) {
     std::unique_ptr<kv_release> r(new kv_release);
@@ -352,6 +393,16 @@ int kv_helm_template(const char *chart_dir, const char *release_name, const char
 int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *release_names, const char *ns,
                       const kv_overrides *overrides, char **out, int64_t *out_off) {
     if (!chart || n_releases < 0 || !out || !out_off) return fail(KV_EINVAL, "null argument");
+    const bool trace = getenv("KVEDGE_TRACE") && atoi(getenv("KVEDGE_TRACE")) > 0;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_start = now();
+    double t_prev = t_start;
+    auto lap = [&](const char *what) {
+        if (!trace) return;
+        const double t = now();
+        fprintf(stderr, "kv_fleet_template: %-28s %8.3f ms\n", what, t - t_prev);
+        t_prev = t;
+    };
     std::vector<std::unique_ptr<kv_release>> rel((size_t)n_releases);
     {
         // Installs are independent: plan them on all host threads (the templates are parsed
@@ -390,46 +441,57 @@ int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *
         for (auto &t : pool) t.join();
         if (first_rc.load() != KV_OK) return fail(first_rc.load(), err_msg);
     }
-    // one packed batch over every pending Secret payload of the fleet
-    std::vector<int64_t> in_off(1, 0), enc_off(1, 0);
-    size_t total_in = 0;
-    for (auto &r : rel)
-        for (auto &p : r->pending) {
-            total_in += p.input.size();
-            in_off.push_back((int64_t)total_in);
-            enc_off.push_back(enc_off.back() + (int64_t)((p.encoded_len + 15) / 16 * 16));
-        }
-    const int64_t n_units = (int64_t)in_off.size() - 1;
-    std::string blob;
-    blob.reserve(total_in);
-    for (auto &r : rel)
-        for (auto &p : r->pending) blob += p.input;
-    std::string enc((size_t)enc_off.back(), '\0');
-    if (n_units > 0) {
-        int rc = kv_b64enc_batch(reinterpret_cast<const uint8_t *>(blob.data()), in_off.data(), n_units, &enc[0],
-                                 enc_off.data());
-        if (rc) return rc;
+    lap("plan (all host threads)");
+    // One packed batch over every pending Secret payload of the fleet.  A placeholder is exactly
+    // as long as its encoding, so every manifest already has its final size: the output buffer is
+    // laid out before anything is encoded, and all copying is done by all host threads.
+    std::vector<size_t> man_off((size_t)n_releases + 1, 0), unit_base((size_t)n_releases + 1, 0);
+    for (int i = 0; i < n_releases; ++i) {
+        man_off[(size_t)i + 1] = man_off[(size_t)i] + rel[(size_t)i]->manifest.size();
+        unit_base[(size_t)i + 1] = unit_base[(size_t)i] + rel[(size_t)i]->pending.size();
     }
-    size_t u = 0, total_out = 0;
-    for (auto &r : rel) {
-        for (size_t i = 0; i < r->pending.size(); ++i, ++u)
-            r->filled[i].assign(enc, (size_t)enc_off[u], r->pending[i].encoded_len);
-        r->n_filled = r->pending.size();
-        splice(r->manifest, r->pending, r->filled);
-        r->spliced = true;
-        total_out += r->manifest.size();
+    const int64_t n_units = (int64_t)unit_base[(size_t)n_releases];
+    std::vector<int64_t> in_off((size_t)n_units + 1, 0), enc_off((size_t)n_units + 1, 0);
+    {
+        size_t u = 0;
+        for (auto &r : rel)
+            for (auto &p : r->pending) {
+                in_off[u + 1] = in_off[u] + (int64_t)p.input.size();
+                enc_off[u + 1] = enc_off[u] + (int64_t)((p.encoded_len + 15) / 16 * 16);
+                ++u;
+            }
     }
+    const size_t total_out = man_off[(size_t)n_releases];
+    static std::mutex stage_mu;   // the staging buffers are one per process
+    std::lock_guard<std::mutex> stage_lock(stage_mu);
+    char *stage_in = nullptr, *stage_out = nullptr;
+    int rc = kv_stage_get_((size_t)in_off[(size_t)n_units], (size_t)enc_off[(size_t)n_units], &stage_in, &stage_out);
+    if (rc) return rc;
     char *buf = static_cast<char *>(malloc(total_out + 1));
     if (!buf) return fail(KV_ENOMEM, "malloc");
-    size_t pos = 0;
-    for (int i = 0; i < n_releases; ++i) {
-        out_off[i] = (int64_t)pos;
-        memcpy(buf + pos, rel[(size_t)i]->manifest.data(), rel[(size_t)i]->manifest.size());
-        pos += rel[(size_t)i]->manifest.size();
+    parallel_for(n_releases, [&](int i) {
+        kv_release &r = *rel[(size_t)i];
+        size_t u = unit_base[(size_t)i];
+        for (auto &p : r.pending) memcpy(stage_in + in_off[u++], p.input.data(), p.input.size());
+        memcpy(buf + man_off[(size_t)i], r.manifest.data(), r.manifest.size());
+    });
+    lap("pack inputs, lay out manifests");
+    if (n_units > 0) {
+        rc = kv_b64enc_batch(reinterpret_cast<const uint8_t *>(stage_in), in_off.data(), n_units, stage_out, enc_off.data());
+        if (rc) {
+            free(buf);
+            return rc;
+        }
     }
-    out_off[n_releases] = (int64_t)pos;
-    buf[pos] = 0;
+    lap("kv_b64enc_batch");
+    parallel_for(n_releases, [&](int i) {
+        kv_release &r = *rel[(size_t)i];
+        splice_raw(buf + man_off[(size_t)i], r.manifest.size(), r.pending, stage_out, &enc_off[unit_base[(size_t)i]]);
+    });
+    for (int i = 0; i <= n_releases; ++i) out_off[i] = (int64_t)man_off[(size_t)i];
+    buf[total_out] = 0;
     *out = buf;
+    lap("splice");
     return KV_OK;
 }
 
