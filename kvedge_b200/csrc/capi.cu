@@ -200,9 +200,12 @@ void trace_dump() {
 // The tile table is built here on the host (every offset is known) and travels with the
 // offsets in a single copy: per chunk the GPU sees one control copy, one data copy, the
 // encode (or decode) kernel and one copy back.
+// lone: the chunk is the whole batch (a single render, a handful of Secrets).  Nothing can
+// overlap then, so everything goes down ONE stream with no events in between, and a small input
+// rides in the control block's copy: latency is all such a call has.
 int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *out,
               const int64_t *out_off, int64_t lo, int64_t hi, int64_t *out_len,
-              int64_t *status, int sm_count) {
+              int64_t *status, int sm_count, bool lone) {
     int rc;
     // the previous chunk in this slot: its uploads must be over before h_ctl is rewritten
     // (long past), and its downloads before the device buffers are written again (ordered on
@@ -215,15 +218,16 @@ int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *ou
     // keep each unit's alignment (mod 16) identical on the device and on the host side
     // and give the device side of each copy the host side's offset inside a 4 KiB page: the copy
     // engines run measurably below their rate when source and destination are skewed
-    const int64_t ishift = (int64_t)(reinterpret_cast<uintptr_t>(in + ibeg) & 4095u);
+    const bool inline_input = lone && in_bytes <= (48 << 10);
+    const int64_t ishift = inline_input ? 16 : (int64_t)(reinterpret_cast<uintptr_t>(in + ibeg) & 4095u);
     const int64_t oshift = (int64_t)(reinterpret_cast<uintptr_t>(out + obeg) & 4095u);
     const int tile = mode == 0 ? kvedge::kEncTileIn : kvedge::dec_tile_in();
     const kvedge::ScratchLayout L = kvedge::scratch_layout(n, in_bytes + ishift, tile);
     const size_t off_in = 0, off_out = (size_t)(n + 1) * 8, off_len = off_out + (size_t)(n + 1) * 8;
     const size_t off_status = off_len + (size_t)n * 8;
     const size_t off_scratch = (off_status + (size_t)n * 8 + 255) / 256 * 256;
-    const size_t ctl_total = off_scratch + L.total;
-    if ((rc = grow(&s.d_in, &s.cap_in, (size_t)(in_bytes + ishift + 32)))) return rc;
+    const size_t ctl_total = off_scratch + L.total + (inline_input ? (size_t)in_bytes + 512 : 0);
+    if (!inline_input && (rc = grow(&s.d_in, &s.cap_in, (size_t)(in_bytes + ishift + 32)))) return rc;
     if ((rc = grow(&s.d_out, &s.cap_out, (size_t)(out_bytes + oshift + 32)))) return rc;
     if ((rc = grow(&s.d_ctl, &s.cap_ctl, ctl_total))) return rc;
     if ((rc = grow_pinned(&s.h_ctl, &s.cap_hctl, ctl_total))) return rc;
@@ -240,12 +244,20 @@ int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *ou
                                                     s.h_ctl + off_scratch,
                                                     reinterpret_cast<const int64_t *>(s.d_ctl + off_out),
                                                     h_len, h_status);
-    const size_t ctl_used = off_scratch + L.desc_off + (size_t)n_tiles * sizeof(kvedge::TileDesc);
-    cudaStream_t s_up = g_ctx.s_up, s_run = g_ctx.s_run, s_down = g_ctx.s_down;
+    size_t ctl_used = off_scratch + L.desc_off + (size_t)n_tiles * sizeof(kvedge::TileDesc);
+    const char *d_input = s.d_in;
+    if (inline_input) {
+        const size_t data_base = (ctl_used + 255) / 256 * 256;
+        memcpy(s.h_ctl + data_base + ishift, in + ibeg, (size_t)in_bytes);
+        d_input = s.d_ctl + data_base;
+        ctl_used = data_base + (size_t)ishift + (size_t)in_bytes;
+    }
+    cudaStream_t s_run = g_ctx.s_run;
+    cudaStream_t s_up = lone ? s_run : g_ctx.s_up, s_down = lone ? s_run : g_ctx.s_down;
     if (s.used) KV_CUDA(cudaStreamWaitEvent(s_up, s.down, 0));
     trace_mark(0, s_up);
     KV_CUDA(cudaMemcpyAsync(s.d_ctl, s.h_ctl, ctl_used, cudaMemcpyHostToDevice, s_up));
-    if (in_bytes > 0) {
+    if (in_bytes > 0 && !inline_input) {
         // An upload whose host address is not 256-byte aligned runs ~10 % slower and drags the
         // concurrent download with it (tools/pcie_peak.py): send the ragged head on its own.
         size_t head = (size_t)((256u - (reinterpret_cast<uintptr_t>(in + ibeg) & 255u)) & 255u);
@@ -256,7 +268,7 @@ int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *ou
     }
     trace_mark(1, s_up);
     KV_CUDA(cudaEventRecord(s.up, s_up));
-    KV_CUDA(cudaStreamWaitEvent(s_run, s.up, 0));
+    if (!lone) KV_CUDA(cudaStreamWaitEvent(s_run, s.up, 0));
     const int64_t *d_in_off = reinterpret_cast<const int64_t *>(s.d_ctl + off_in);
     const int64_t *d_out_off = reinterpret_cast<const int64_t *>(s.d_ctl + off_out);
     int64_t *d_len = reinterpret_cast<int64_t *>(s.d_ctl + off_len);
@@ -266,18 +278,18 @@ int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *ou
     if (diag < 0) { const char *d = getenv("KVEDGE_E2E_DIAG"); diag = d ? atoi(d) : 0; }
     if (n_tiles > 0 && diag == 0) {
         if (mode == 0)
-            e = kvedge::launch_b64enc_run(reinterpret_cast<const uint8_t *>(s.d_in), d_in_off, n,
+            e = kvedge::launch_b64enc_run(reinterpret_cast<const uint8_t *>(d_input), d_in_off, n,
                                           in_bytes + ishift, s.d_out, s.d_ctl + off_scratch, L.total,
                                           s_run, sm_count);
         else
-            e = kvedge::launch_b64dec_run(s.d_in, d_in_off, n, in_bytes + ishift,
+            e = kvedge::launch_b64dec_run(d_input, d_in_off, n, in_bytes + ishift,
                                           reinterpret_cast<uint8_t *>(s.d_out), d_out_off, d_len, d_status,
                                           s.d_ctl + off_scratch, L.total, s_run, sm_count);
     }
     if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
     trace_mark(2, s_run);
     KV_CUDA(cudaEventRecord(s.ran, s_run));
-    if (diag != 2) KV_CUDA(cudaStreamWaitEvent(s_down, s.ran, 0));
+    if (diag != 2 && !lone) KV_CUDA(cudaStreamWaitEvent(s_down, s.ran, 0));
     if (out_bytes > 0)
         KV_CUDA(cudaMemcpyAsync(out + obeg, s.d_out + oshift, (size_t)out_bytes, cudaMemcpyDeviceToHost, s_down));
     if (mode == 1) {
@@ -314,19 +326,22 @@ int run_host_batch(int mode, const char *in, const int64_t *in_off, int64_t n_un
     if ((rc = sm_count_of_current_device(&sms))) return rc;
     int64_t lo = 0;
     int turn = 0;
+    bool all_lone = true;
     while (lo < n_units) {
         int64_t hi = lo + 1;
         while (hi < n_units && in_off[hi + 1] - in_off[lo] <= chunk_bytes()) ++hi;
+        all_lone = all_lone && lo == 0 && hi == n_units;
         rc = run_chunk(g_ctx.slot[turn % n_slots()], mode, in, in_off, out, out_off, lo, hi, out_len,
-                       status, sms);
+                       status, sms, lo == 0 && hi == n_units);
         if (rc) break;
         lo = hi;
         ++turn;
     }
-    // everything a chunk does ends in the download stream
-    cudaError_t e1 = cudaStreamSynchronize(g_ctx.s_down);
+    // everything a chunk does ends in the download stream (a lone chunk: in the kernel stream)
+    const bool was_lone = all_lone;
     cudaError_t e2 = cudaStreamSynchronize(g_ctx.s_run);
-    cudaError_t e3 = cudaStreamSynchronize(g_ctx.s_up);
+    cudaError_t e1 = was_lone ? cudaSuccess : cudaStreamSynchronize(g_ctx.s_down);
+    cudaError_t e3 = was_lone ? cudaSuccess : cudaStreamSynchronize(g_ctx.s_up);
     if (!rc && e1 != cudaSuccess) rc = cuda_fail(e1, "download stream");
     if (!rc && e2 != cudaSuccess) rc = cuda_fail(e2, "kernel stream");
     if (!rc && e3 != cudaSuccess) rc = cuda_fail(e3, "upload stream");
