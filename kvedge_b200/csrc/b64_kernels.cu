@@ -10,12 +10,14 @@
 // Shape of the work: many independent units (one Secret payload each) of ragged
 // length in one packed blob.  It is HBM-bound byte work -- 1 byte read and 4/3 bytes
 // written per input byte -- so the design goals are coalesced 16-byte stores, enough
-// bytes in flight per SM, and an ALU/FMA-pipe balanced sextet->ASCII mapping with no
-// table lookups.  No tensor cores: nothing here is a GEMM.
+// bytes in flight per SM (bulk async copies into shared-memory rings), and a sextet->ASCII
+// mapping balanced over the ALU, FMA and load/store pipes.  No tensor cores: nothing here
+// is a GEMM.
 //
-//   plan_count / plan_emit   ragged units -> fixed-size tiles (TileDesc table in scratch)
-//   b64enc_tiles             persistent grid, one tile per block iteration
-//   b64dec_tiles             canonical input fast path; anything else is flagged ...
+//   plan_count / plan_emit   ragged units -> tiles (TileDesc table in scratch)
+//   b64enc_groups            encode: one block per SM, five producer/consumer pipelines
+//   b64enc_stream            encode: one pipeline per block (tiny batches; earlier product)
+//   b64dec_stream            decode of canonical input; anything else is flagged ...
 //   b64dec_slow              ... and re-decoded sequentially with Go's exact semantics
 #include "b64_kernels.cuh"
 
@@ -401,156 +403,6 @@ __device__ __noinline__ void encode_bytes(const uint8_t *p, char *q, int nvalid)
         v = make_uint4(w[0], w[1], w[2], w[3]);
     }
     store_chars(q, v, (nvalid + 2) / 3 * 4);
-}
-
-// One tile, one warp: lane l of iteration i takes input bytes [384 i + 12 l, +12) and
-// writes output bytes [512 i + 16 l, +16), so a warp reads 384 contiguous bytes and
-// stores 512 contiguous bytes per iteration.
-//   SHIFTED  the tile's first byte is not 4-byte aligned: one more word per lane and
-//            a funnel shift (the shift amount is uniform over the tile);
-//   VEC16    the destination is 16-byte aligned: one STG.128 per lane, else four STG.32.
-// The unit's last lane (fewer than 12 bytes left) masks the bytes that are not its own,
-// patches in the '=' padding and stores only its 4, 8 or 12 characters.
-template <bool SHIFTED, bool VEC16, bool PIPE, int NLUT>
-__device__ __forceinline__ void encode_tile_warp(const uint8_t *src, char *dst, int len,
-                                                 uint32_t sh, int lane, const uint16_t *lut) {
-    if (NLUT == -2) {
-        // diagnostic skeleton 2: fully coalesced 16-byte loads (24 lanes cover the 384 input
-        // bytes of an iteration), 16-byte stores, no arithmetic; bytes are wrong on purpose
-        const uint4 *vp = reinterpret_cast<const uint4 *>(src - (reinterpret_cast<uintptr_t>(src) & 15)) + lane;
-        char *q2 = dst + lane * 16;
-        uint4 nv = make_uint4(0, 0, 0, 0);
-        if (lane < 24) nv = __ldg(vp);
-        for (int o = 0; o < len; o += 384, q2 += 512) {
-            const uint4 v = nv;
-            vp += 24;
-            if (o + 384 < len && lane < 24) nv = __ldg(vp);
-            if (o + lane * 12 + 12 <= len) *reinterpret_cast<uint4 *>(q2) = v;
-        }
-        return;
-    }
-    const uint32_t *wp = reinterpret_cast<const uint32_t *>(src - sh) + lane * 3;
-    char *q = dst + lane * 16;
-    const uint32_t s8 = sh * 8;
-    int off = lane * 12;
-    if (off >= len) return;
-    // software pipeline: the next iteration's words are requested before this one's are used
-    uint32_t n0 = 0, n1 = 0, n2 = 0, n3 = 0;
-    if (PIPE) {
-        n0 = __ldg(wp); n1 = __ldg(wp + 1); n2 = __ldg(wp + 2);
-        if (SHIFTED) n3 = __ldg(wp + 3);
-    }
-    for (; off < len; off += 384, q += 512) {
-        uint32_t a0, a1, a2, a3 = 0;
-        if (PIPE) {
-            a0 = n0; a1 = n1; a2 = n2; a3 = n3;
-            wp += 96;
-            if (off + 384 < len) {
-                n0 = __ldg(wp); n1 = __ldg(wp + 1); n2 = __ldg(wp + 2);
-                if (SHIFTED) n3 = __ldg(wp + 3);
-            }
-        } else {
-            a0 = __ldg(wp); a1 = __ldg(wp + 1); a2 = __ldg(wp + 2);
-            if (SHIFTED) a3 = __ldg(wp + 3);
-            wp += 96;
-        }
-        if (SHIFTED) {
-            a0 = __funnelshift_r(a0, a1, s8);
-            a1 = __funnelshift_r(a1, a2, s8);
-            a2 = __funnelshift_r(a2, a3, s8);
-        }
-        const int left = len - off;
-        if (left >= 12) {
-            const uint4 v = encode12_mixed<NLUT>(a0, a1, a2, lut);
-            if (VEC16) {
-                *reinterpret_cast<uint4 *>(q) = v;
-            } else {
-                uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
-                q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
-            }
-        } else {
-            // tail of the unit: 1..11 bytes are ours, the rest of the words is not
-            const uint32_t keep = 0xFFFFFFFFu >> (8 * (3 - ((left - 1) & 3)));
-            if (left <= 4) { a0 &= keep; a1 = 0u; a2 = 0u; }
-            else if (left <= 8) { a1 &= keep; a2 = 0u; }
-            else { a2 &= keep; }
-            const uint4 v = encode12(a0, a1, a2);
-            uint32_t w[4] = {v.x, v.y, v.z, v.w};
-            const int rem = left % 3, gi = left / 3;
-            if (rem) {
-#pragma unroll
-                for (int g = 0; g < 4; ++g)
-                    if (g == gi)
-                        w[g] = (rem == 1) ? ((w[g] & 0x0000FFFFu) | 0x3D3D0000u)
-                                          : ((w[g] & 0x00FFFFFFu) | 0x3D000000u);
-            }
-            const int nwords = (left + 2) / 3;
-            uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
-#pragma unroll
-            for (int g = 0; g < 4; ++g)
-                if (g < nwords) q4[g] = w[g];
-        }
-    }
-}
-
-// Persistent grid of independent warps: each warp pulls whole tiles (one contiguous piece
-// of one unit, at most 12 KiB) from a counter in the scratch header, so ragged units -- an
-// 11 KiB config next to a 2.4 KB cloud-init text -- spread evenly and no block-wide
-// barrier is ever needed.  header: [0] n_tiles, [1] next tile, [2] warps finished (the
-// last one re-arms [1] and [2] for the next launch over the same plan).
-template <int MIN_BLOCKS, bool PIPE, int NLUT>
-__global__ void __launch_bounds__(kThreads, MIN_BLOCKS)
-b64enc_tiles(const uint8_t *__restrict__ in, char *__restrict__ out,
-             const TileDesc *__restrict__ desc, int *__restrict__ header,
-             const int64_t *__restrict__ in_off, int64_t n_units) {
-    __shared__ uint16_t lut_s[NLUT > 0 ? 4096 : 1];  // NLUT < 0: diagnostic skeleton
-    const uint16_t *lut = lut_s;
-    if (NLUT > 0) {
-        fill_pair_lut(lut_s);
-        __syncthreads();
-    }
-    const int lane = threadIdx.x & 31;
-    const int n_warps = (int)(gridDim.x * (kThreads / 32));
-    const int n_tiles = header[0];
-    const int64_t in_end = in_off[n_units];
-    int tile = (int)(blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5));  // first tile: static
-    while (tile < n_tiles) {
-        int next = 0;
-        if (lane == 0) next = atomicAdd(&header[1], 1) + n_warps;  // in flight during the tile
-        const int4 *dp = reinterpret_cast<const int4 *>(desc + tile);
-        const int4 d0 = __ldg(dp), d1 = __ldg(dp + 1);
-        const int64_t in_pos = ((int64_t)(uint32_t)d0.y << 32) | (uint32_t)d0.x;
-        const int64_t out_pos = ((int64_t)(uint32_t)d0.w << 32) | (uint32_t)d0.z;
-        const int len = d1.x;
-        const uint8_t *src = in + in_pos;
-        char *dst = out + out_pos;
-        const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 3u);
-        const uint32_t dalign = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
-        // Word loads touch up to 3 bytes before and 4 after a lane's 12 bytes: only take
-        // the word path when that stays inside the blob for the whole tile.
-        const bool words_ok = in_pos >= 3 && in_pos + len + 4 <= in_end && (dalign & 3u) == 0;
-        if (words_ok) {
-            if (dalign == 0) {
-                if (sh == 0) encode_tile_warp<false, true, PIPE, NLUT>(src, dst, len, sh, lane, lut);
-                else encode_tile_warp<true, true, PIPE, NLUT>(src, dst, len, sh, lane, lut);
-            } else {
-                if (sh == 0) encode_tile_warp<false, false, PIPE, NLUT>(src, dst, len, sh, lane, lut);
-                else encode_tile_warp<true, false, PIPE, NLUT>(src, dst, len, sh, lane, lut);
-            }
-        } else {
-            for (int off = lane * 12; off < len; off += 384)
-                encode_bytes(src + off, dst + off / 3 * 4, (len - off) < 12 ? (len - off) : 12);
-        }
-        tile = __shfl_sync(0xffffffffu, next, 0);
-    }
-    if (lane == 0) {
-        __threadfence();
-        if (atomicAdd(&header[2], 1) == n_warps - 1) {
-            header[1] = 0;
-            header[2] = 0;
-            __threadfence();
-        }
-    }
 }
 
 // ----------------------------------------------------------------------------- encode, streamed
@@ -1674,107 +1526,6 @@ __device__ __forceinline__ uint32_t dec6(uint32_t c) {
     return v;
 }
 
-// Four characters (little-endian word) -> 24-bit group as bytes b0 | b1<<8 | b2<<16;
-// bit 31 of the result is set if any character was outside the alphabet.
-__device__ __forceinline__ uint32_t decode4(uint32_t w) {
-    uint32_t v0 = dec6(w & 0xFFu), v1 = dec6((w >> 8) & 0xFFu);
-    uint32_t v2 = dec6((w >> 16) & 0xFFu), v3 = dec6(w >> 24);
-    uint32_t bad = (v0 | v1 | v2 | v3) & 0x80u;
-    uint32_t n = (v0 << 18) | (v1 << 12) | (v2 << 6) | v3;  // 24-bit big-endian value
-    uint32_t r = __byte_perm(n, 0u, 0x4012);                 // -> b0 | b1<<8 | b2<<16
-    return r | (bad << 24);
-}
-
-__global__ void __launch_bounds__(kThreads)
-b64dec_tiles(const char *__restrict__ in, uint8_t *__restrict__ out,
-             const TileDesc *__restrict__ desc, const int *__restrict__ header,
-             const int64_t *__restrict__ in_off, int64_t n_units,
-             int64_t *__restrict__ out_len, int64_t *__restrict__ status) {
-    const int n_tiles = header[0];
-    const int64_t in_end = in_off[n_units];
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const int4 *dp = reinterpret_cast<const int4 *>(desc + tile);
-        const int4 d0 = __ldg(dp), d1 = __ldg(dp + 1);
-        const int64_t in_pos = ((int64_t)(uint32_t)d0.y << 32) | (uint32_t)d0.x;
-        const int64_t out_pos = ((int64_t)(uint32_t)d0.w << 32) | (uint32_t)d0.z;
-        const int len = d1.x;
-        const int unit = d1.y;
-        const bool last_tile = (d1.z & 1) != 0;
-        const uint8_t *src = reinterpret_cast<const uint8_t *>(in) + in_pos;
-        uint8_t *dst = out + out_pos;
-        const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 3u);
-        const bool dst4 = (reinterpret_cast<uintptr_t>(dst) & 3u) == 0;
-        if (len & 3) continue;  // unit length not a multiple of 4: plan flagged it (-2)
-#pragma unroll
-        for (int row = 0; row < kDecTileIn / (kThreads * 16); ++row) {
-            const int off = row * (kThreads * 16) + (int)threadIdx.x * 16;
-            if (off >= len) break;
-            const uint8_t *p = src + off;
-            uint8_t *q = dst + (row * (kThreads * 12) + (int)threadIdx.x * 12);
-            const int nvalid = (len - off) < 16 ? (len - off) : 16;  // multiple of 4
-            uint32_t w[4] = {0x41414141u, 0x41414141u, 0x41414141u, 0x41414141u};
-            const bool interior = (nvalid == 16) && (in_pos + off + 20 <= in_end) &&
-                                  (in_pos + off >= 3);
-            if (interior) {
-                const uint32_t *wp = reinterpret_cast<const uint32_t *>(p - sh);
-                w[0] = __ldg(wp); w[1] = __ldg(wp + 1); w[2] = __ldg(wp + 2); w[3] = __ldg(wp + 3);
-                if (sh) {
-                    uint32_t w4 = __ldg(wp + 4);
-                    const uint32_t s8 = sh * 8;
-                    w[0] = __funnelshift_r(w[0], w[1], s8);
-                    w[1] = __funnelshift_r(w[1], w[2], s8);
-                    w[2] = __funnelshift_r(w[2], w[3], s8);
-                    w[3] = __funnelshift_r(w[3], w4, s8);
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 16; ++i)
-                    if (i < nvalid) {
-                        uint32_t m = 0xFFu << (8 * (i & 3));
-                        w[i >> 2] = (w[i >> 2] & ~m) | ((uint32_t)p[i] << (8 * (i & 3)));
-                    }
-            }
-            // '=' padding is legal only in the last quantum of the unit.
-            int npad = 0;
-            const int nq = nvalid >> 2;
-            if (last_tile && off + nvalid == len) {
-#pragma unroll
-                for (int g = 0; g < 4; ++g)
-                    if (g == nq - 1) {
-                        if ((w[g] >> 24) == 0x3Du) {
-                            npad = 1;
-                            w[g] = (w[g] & 0x00FFFFFFu) | 0x41000000u;
-                            if (((w[g] >> 16) & 0xFFu) == 0x3Du) {
-                                npad = 2;
-                                w[g] = (w[g] & 0xFF00FFFFu) | 0x00410000u;
-                            }
-                        }
-                    }
-                out_len[unit] = (int64_t)(in_pos - in_off[unit] + off + nvalid) / 4 * 3 - npad;
-            }
-            uint32_t g0 = decode4(w[0]), g1 = decode4(w[1]), g2 = decode4(w[2]), g3 = decode4(w[3]);
-            if ((g0 | g1 | g2 | g3) & 0x80000000u) {
-                status[unit] = -2;  // benign race: every writer stores the same value
-                continue;
-            }
-            g0 &= 0xFFFFFFu; g1 &= 0xFFFFFFu; g2 &= 0xFFFFFFu; g3 &= 0xFFFFFFu;
-            const uint32_t o0 = g0 | (g1 << 24);
-            const uint32_t o1 = (g1 >> 8) | (g2 << 16);
-            const uint32_t o2 = (g2 >> 16) | (g3 << 8);
-            const int nbytes = nq * 3 - npad;
-            if (dst4 && nbytes == 12) {
-                uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
-                q4[0] = o0; q4[1] = o1; q4[2] = o2;
-            } else {
-                const uint32_t o[3] = {o0, o1, o2};
-#pragma unroll
-                for (int i = 0; i < 12; ++i)
-                    if (i < nbytes) q[i] = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
-            }
-        }
-    }
-}
-
 // Sequential decode of the units the fast path flagged (status == -2): '\r'/'\n'
 // inside the text, padding in odd places, characters outside the alphabet, lengths
 // that are not a multiple of four.  Follows Go's encoding/base64 decodeQuantum
@@ -1904,7 +1655,7 @@ int64_t plan_tiles_host(const int64_t *in_off, const int64_t *out_off, int64_t n
 }
 
 // ----------------------------------------------------------------------------- launchers
-static int g_occ_enc = 0, g_occ_dec = 0;
+static int g_occ_dec = 0;
 
 static cudaError_t plan(const int64_t *d_in_off, const int64_t *d_out_off, int64_t n_units,
                         int tile_in, int small_max, int mode, const ScratchLayout &L, void *d_scratch,
@@ -1957,14 +1708,9 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
     ScratchLayout L = scratch_layout(n_units, total_in_bytes, kEncTileIn);
     if (scratch_bytes < L.total) return cudaErrorInvalidValue;
     using EncKernel = void (*)(const uint8_t *, char *, const TileDesc *, int *, const int64_t *, int64_t);
-    // variant 0 is the product kernel; the rest are tuning / diagnostic builds for tools/sweep_enc.py
-    static const EncKernel kVariants[] = {b64enc_tiles<8, true, 2>, b64enc_tiles<8, true, 0>,
-                                          b64enc_tiles<8, false, 0>, b64enc_tiles<8, true, 1>,
-                                          b64enc_tiles<8, true, 3>, b64enc_tiles<6, true, 2>,
-                                          b64enc_tiles<8, true, -1>, b64enc_tiles<8, true, -2>};
     // The product kernel is the grouped one (200); a tiny batch (a single render) takes the
     // one-pipeline, all-arithmetic build below, which has no table to fill.  KVEDGE_ENC_VARIANT=1..
-    // selects the one-pipeline-per-block kernels, 100.. the load/store kernels, 201.. other group shapes.
+    // selects the one-pipeline-per-block kernels, 201.. other group shapes.
     int variant = enc_variant_for(L);
     cudaError_t e;
     if (variant >= 200) {  // grouped pipelines: several producer/consumer groups per block around one table
@@ -2008,7 +1754,7 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
                                    reinterpret_cast<const TileDesc *>(base + L.desc_off), reinterpret_cast<int *>(base),
                                    d_in_off, n_units);
     }
-    if (variant < 100) {  // streamed (bulk-copy ring) kernels; variant 0 is the product kernel
+    {   // one pipeline per block: tiny batches, and KVEDGE_ENC_VARIANT=1..17 for tools/sweep_enc.py
         struct StreamVariant { EncKernel fn; int stages, consumers, ring; };
         static const StreamVariant kStream[] = {
             {stream::b64enc_stream<3, 8, 2, 4>, 3, 8},  {stream::b64enc_stream<4, 8, 2, 3>, 4, 8},
@@ -2052,23 +1798,7 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
             reinterpret_cast<int *>(base), d_in_off, n_units);
         return cudaGetLastError();
     }
-    variant -= 100;  // 100.. : the load/store (non-streamed) kernels kept for comparison
-    if (variant < 0 || variant >= (int)(sizeof kVariants / sizeof *kVariants)) variant = 0;
-    EncKernel kern = kVariants[variant];
-    if (g_occ_enc == 0) {
-        int occ = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, 0);
-        if (e != cudaSuccess) return e;
-        g_occ_enc = occ > 0 ? occ : 1;
-    }
-    int64_t grid = (int64_t)sm_count * g_occ_enc;
-    if (grid > L.max_tiles) grid = L.max_tiles;
-    if (grid < 1) grid = 1;
-    char *base = static_cast<char *>(d_scratch);
-    kern<<<(unsigned)grid, kThreads, 0, stream>>>(
-        d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
-        reinterpret_cast<int *>(base), d_in_off, n_units);
-    return cudaGetLastError();
+    return cudaErrorInvalidValue;   // not reached: every variant was handled above
 }
 
 cudaError_t launch_b64enc(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
@@ -2083,7 +1813,7 @@ cudaError_t launch_b64enc(const uint8_t *d_in, const int64_t *d_in_off, int64_t 
 }
 
 // The streamed decode kernel's shapes.  Entry 0 is the product; the others are kept for
-// tools/sweep_dec.py (KVEDGE_DEC_VARIANT=n), 100 selects the older load/store kernel.
+// tools/sweep_dec.py (KVEDGE_DEC_VARIANT=n).
 using DecKernel = void (*)(const char *, uint8_t *, const TileDesc *, int *, const int64_t *, int64_t,
                            int64_t *, int64_t *);
 struct DecVariant { DecKernel fn; int groups, stages, consumers, tile, ring; };
@@ -2101,14 +1831,14 @@ static int dec_variant() {
     if (v < 0) {
         const char *e = getenv("KVEDGE_DEC_VARIANT");
         int x = e ? atoi(e) : 0;
-        if (x < 0 || (x < 100 && x >= (int)(sizeof kDec / sizeof *kDec))) x = 0;
+        if (x < 0 || x >= (int)(sizeof kDec / sizeof *kDec)) x = 0;
         v = x;
     }
     return v;
 }
 
-int dec_tile_in() { return dec_variant() < 100 ? kDec[dec_variant()].tile : kDecTileIn; }
-int dec_small_max() { return dec_variant() < 100 ? dec_tile_in() / 4 : 0; }
+int dec_tile_in() { return kDec[dec_variant()].tile; }
+int dec_small_max() { return dec_tile_in() / 4; }
 
 cudaError_t launch_b64dec(const char *d_in, const int64_t *d_in_off, int64_t n_units,
                           int64_t total_in_bytes, uint8_t *d_out, const int64_t *d_out_off,
@@ -2136,7 +1866,7 @@ cudaError_t launch_b64dec_run(const char *d_in, const int64_t *d_in_off, int64_t
     cudaError_t e;
     const int variant = dec_variant();
     char *base = static_cast<char *>(d_scratch);
-    if (variant < 100) {
+    {
         const DecVariant &dv = kDec[variant];
         const int threads = 32 * dv.groups * (1 + dv.consumers);
         const size_t dyn = (size_t)stream::kDecLutBytes + (size_t)dv.groups * (dv.ring ? (size_t)dv.ring : (size_t)dv.stages * stream::dec_stage_stride(dv.tile));
@@ -2163,19 +1893,6 @@ cudaError_t launch_b64dec_run(const char *d_in, const int64_t *d_in_off, int64_t
                                 reinterpret_cast<const TileDesc *>(base + L.desc_off), reinterpret_cast<int *>(base),
                                 d_in_off, n_units, d_out_len, d_status);
         if (e != cudaSuccess) return e;
-    } else {
-        if (g_occ_dec == 0) {
-            int occ = 0;
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, b64dec_tiles, kThreads, 0);
-            if (e != cudaSuccess) return e;
-            g_occ_dec = occ > 0 ? occ : 1;
-        }
-        int64_t grid = (int64_t)sm_count * g_occ_dec;
-        if (grid > L.max_tiles) grid = L.max_tiles;
-        if (grid < 1) grid = 1;
-        b64dec_tiles<<<(unsigned)grid, kThreads, 0, stream>>>(
-            d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
-            reinterpret_cast<const int *>(base), d_in_off, n_units, d_out_len, d_status);
     }
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Kernel timing of the decode path (plan + b64dec_tiles + b64dec_slow) on the encoded bench fleet."""
+"""Kernel timing of the decode path (plan + b64dec_stream + b64dec_slow) on the encoded bench fleet."""
 import json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Kernel-only timing of b64enc_tiles on the bench fleet for one KVEDGE_ENC_VARIANT
+"""Kernel-only timing of the encode kernel on the bench fleet for one KVEDGE_ENC_VARIANT
 (run once per variant: the variant is latched at first launch).  Prints one JSON line."""
 import json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
