@@ -300,3 +300,35 @@ def test_group_tiles_decode_clean_and_corrupt(torch_cuda, align):
         a = out[int(dec_off[i]):int(dec_off[i]) + int(out_len[i])]
         b = ref_out[int(dec_off[i]):int(dec_off[i]) + int(ref_len[i])]
         assert np.array_equal(a, b), i
+
+
+def test_concurrent_callers_are_serialised_not_corrupted(torch_cuda):
+    """ctypes drops the GIL during a call, so these really do enter the library concurrently."""
+    import threading
+    rng = np.random.default_rng(99)
+    jobs = []
+    for t in range(4):
+        units = [rng.bytes(int(s)) for s in rng.integers(0, 20000, 200)]
+        jobs.append((units, [ob64.encode(u) for u in units]))
+    errors = []
+
+    def worker(units, expect):
+        try:
+            for _ in range(10):
+                if b64.b64enc_many(units) != expect:
+                    errors.append("mismatch")
+                    return
+                enc = [e for e in expect]
+                if b64.b64dec_many(enc) != units:
+                    errors.append("decode mismatch")
+                    return
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=worker, args=j) for j in jobs]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join(timeout=300)
+    assert not any(th.is_alive() for th in threads), "a caller hung"
+    assert not errors, errors

@@ -11,6 +11,12 @@ installs = int(os.environ.get("INSTALLS", bench.DEFAULT_INSTALLS))
 blob, in_off = bench.build_fleet(installs, 0)
 n = len(in_off) - 1
 lens = np.diff(in_off)
+if os.environ.get("ROUND12"):   # every encoding a multiple of 16 characters: all units start 16-byte aligned
+    keep = lens // 12 * 12
+    idx = np.repeat(in_off[:-1], keep) + (np.arange(int(keep.sum())) - np.repeat(np.cumsum(keep) - keep, keep))
+    blob = blob[idx]
+    lens = keep
+    in_off = np.zeros(n + 1, dtype=np.int64); np.cumsum(lens, out=in_off[1:])
 enc_len = (lens + 2) // 3 * 4
 align = int(os.environ.get("ENC_ALIGN", "16"))
 enc_off = np.zeros(n + 1, dtype=np.int64); np.cumsum((enc_len + align - 1) // align * align, out=enc_off[1:])
