@@ -77,6 +77,7 @@ __device__ __forceinline__ int warp_incl_scan(int v) {
 
 // Exclusive scan of one int per thread across a 1024-thread block; returns the
 // exclusive prefix and stores the block total in *total.
+static_assert(kPlanBlock == 1024, "the block scans below assume exactly 32 warps per plan block");
 __device__ __forceinline__ int block_excl_scan(int v, int *total) {
     __shared__ int warp_sums[32];
     int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
