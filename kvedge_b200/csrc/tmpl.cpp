@@ -1223,9 +1223,23 @@ std::string TemplateSet::placeholder(size_t id, size_t encoded_len) {
     return s;
 }
 
+// Does s hold a byte the placeholders use (0x01, 0x10-0x1F)?  Every value string of every
+// release goes through here (an 11 KB config.toml each time), eight bytes per step: a byte is
+// 0x01 iff (b ^ 0x01) == 0, and in 0x10-0x1F iff ((b ^ 0x10) & 0xF0) == 0; "some byte of v is
+// zero" is (v - 0x01..01) & ~v & 0x80..80.
 bool TemplateSet::has_sentinel_bytes(const std::string &s) {
-    for (unsigned char c : s)
-        if (c == 0x01 || (c >= 0x10 && c < 0x20)) return true;
+    const unsigned char *p = reinterpret_cast<const unsigned char *>(s.data());
+    size_t n = s.size(), i = 0;
+    const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;
+    for (; i + 8 <= n; i += 8) {
+        uint64_t w;
+        memcpy(&w, p + i, 8);
+        const uint64_t a = w ^ ones;                                   // zero byte <=> 0x01
+        const uint64_t b = (w ^ 0x1010101010101010ull) & 0xF0F0F0F0F0F0F0F0ull;   // zero byte <=> 0x10..0x1F
+        if ((((a - ones) & ~a) | ((b - ones) & ~b)) & highs) return true;
+    }
+    for (; i < n; ++i)
+        if (p[i] == 0x01 || (p[i] >= 0x10 && p[i] < 0x20)) return true;
     return false;
 }
 
