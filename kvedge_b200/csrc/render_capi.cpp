@@ -487,6 +487,7 @@ int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *
     parallel_for(n_releases, [&](int i) {
         kv_release &r = *rel[(size_t)i];
         splice_raw(buf + man_off[(size_t)i], r.manifest.size(), r.pending, stage_out, &enc_off[unit_base[(size_t)i]]);
+        rel[(size_t)i].reset();   // freed here, on this thread, not one by one when the function returns
     });
     for (int i = 0; i <= n_releases; ++i) out_off[i] = (int64_t)man_off[(size_t)i];
     buf[total_out] = 0;
