@@ -157,3 +157,29 @@ def test_reference_name_helper_edge_cases():
         sets = [f"nameOverride={override}"]
         r = _plan_and_fill(REF_CHART, set=sets)
         assert r.manifest() == helmref.helm_template(REF_CHART, set_args=sets), override
+
+
+@pytest.mark.parametrize("byte", [0x01] + list(range(0x10, 0x20)))
+def test_placeholder_byte_anywhere_in_a_value_disables_deferral(byte):
+    """The scan for placeholder bytes reads eight bytes per step: every such byte must be found
+    at every position of a word and in the ragged tail, or a user payload could be mistaken for
+    a pending site."""
+    from kvedge_b200 import _lib
+    have_gpu = _lib.lib().kv_device_count() > 0
+    for length in (1, 7, 8, 9, 15, 16, 17, 63, 64, 65, 1000):
+        for pos in sorted({0, 1, 6, 7, 8, 9, length // 2, length - 2, length - 1} & set(range(length))):
+            payload = bytearray(b"x" * length)
+            payload[pos] = byte
+            if not have_gpu:
+                # immediate evaluation needs the GPU: the loud failure IS the detection
+                with pytest.raises(helm.TemplateError, match="no CPU fallback"):
+                    helm.Chart(FIXTURE).plan("rel", blobs={"runtimeConfig": bytes(payload)})
+                continue
+            r = helm.Chart(FIXTURE).plan("rel", blobs={"runtimeConfig": bytes(payload)})
+            # the payload's own site was encoded on the spot; only the cloud-init site may still pend
+            assert bytes(payload) not in r.pending, (byte, length, pos)
+    # and the neighbours of the range stay deferrable
+    for ok in (0x00, 0x02, 0x0F, 0x20, 0x7F, 0x80, 0x90, 0xFF):
+        payload = bytes([ok]) * 24
+        r = helm.Chart(FIXTURE).plan("rel", blobs={"runtimeConfig": payload})
+        assert payload in r.pending, ok
