@@ -594,8 +594,10 @@ void apply_set_file(Value &values, const std::string &expr) {
     for (const auto &kv : split_set(expr)) assign(values, split_key(kv.first), Value::str(read_file(kv.second)));
 }
 
-void apply_set_blob(Value &values, const std::string &key, const std::string &content) {
-    assign(values, split_key(key), Value::str(content));
+void apply_set_blob(Value &values, const std::string &key, std::string content) {
+    Value v = Value::str(std::string());
+    v.s = std::move(content);
+    assign(values, split_key(key), v);
 }
 
 // ============================================================================ chart

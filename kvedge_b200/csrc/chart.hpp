@@ -22,7 +22,7 @@ Value parse_yaml(const std::string &text, bool json_numbers);
 // pkg/strvals: --set / --set-string expressions (README.md:60) and --set-file.
 void apply_set(Value &values, const std::string &expr, bool force_string);
 void apply_set_file(Value &values, const std::string &expr);                 // key=path
-void apply_set_blob(Value &values, const std::string &key, const std::string &content);
+void apply_set_blob(Value &values, const std::string &key, std::string content);
 
 struct Chart {
     std::string dir;

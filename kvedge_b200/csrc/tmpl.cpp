@@ -1119,12 +1119,15 @@ struct Exec {
             return false;
         if (opt.pending->size() >= TemplateSet::kMaxPending) return false;
         Value in = eval_pipe_prefix(p, p.cmds.size() - 1, dot, sc);
-        std::string s = strval(in);
+        std::string s = in.kind == Value::String ? std::move(in.s) : strval(in);   // a config.toml: do not copy it again
         if (s.empty()) return true;  // b64enc "" == ""
         Pending pd;
         pd.encoded_len = (s.size() + 2) / 3 * 4;
         pd.input = std::move(s);
-        out += TemplateSet::placeholder(opt.pending->size(), pd.encoded_len);
+        // the placeholder (TemplateSet::placeholder) written in place: 4 id bytes, then filler
+        const size_t id = opt.pending->size();
+        for (int k = 0; k < 4; ++k) out.push_back((char)(0x10 + ((id >> (12 - 4 * k)) & 0xF)));
+        out.append(pd.encoded_len - 4, '\x01');
         opt.pending->push_back(std::move(pd));
         return true;
     }
