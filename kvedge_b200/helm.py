@@ -72,7 +72,7 @@ class Chart:
         self.dir = chart_dir
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and _lib is not None:   # at interpreter exit the module may be gone
             _lib.lib().kv_chart_free(self._h)
             self._h = None
 
@@ -118,7 +118,7 @@ class Release:
         self._h = handle
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and _lib is not None:
             _lib.lib().kv_release_free(self._h)
             self._h = None
 
