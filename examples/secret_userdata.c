@@ -34,18 +34,22 @@ int main(int argc, char **argv) {
     if (argc < 2) { fprintf(stderr, "usage: %s FILE...\n", argv[0]); return 2; }
     const int n = argc - 1;
     int64_t *in_off = calloc((size_t)n + 1, sizeof *in_off), *out_off = calloc((size_t)n + 1, sizeof *out_off);
-    unsigned char *blob = NULL;
+    unsigned char **file = calloc((size_t)n, sizeof *file);
     for (int i = 0; i < n; ++i) {
         size_t len;
-        unsigned char *p = slurp(argv[i + 1], &len);
-        if (!p) { fprintf(stderr, "cannot read %s\n", argv[i + 1]); return 2; }
-        blob = realloc(blob, (size_t)in_off[i] + len + 1);
-        memcpy(blob + in_off[i], p, len);
-        free(p);
+        file[i] = slurp(argv[i + 1], &len);
+        if (!file[i]) { fprintf(stderr, "cannot read %s\n", argv[i + 1]); return 2; }
         in_off[i + 1] = in_off[i] + (int64_t)len;
         out_off[i + 1] = out_off[i] + (int64_t)((kv_b64enc_len(len) + 15) / 16 * 16);   /* 16-byte aligned units */
     }
-    char *enc = malloc((size_t)out_off[n] + 1);
+    /* the batch and its encodings live in page-locked memory: the copies then run at the link's rate */
+    unsigned char *blob = kv_pinned_alloc((size_t)in_off[n] + 1);
+    char *enc = kv_pinned_alloc((size_t)out_off[n] + 1);
+    if (!blob || !enc) { fprintf(stderr, "kv_pinned_alloc: %s\n", kv_last_error()); return 1; }
+    for (int i = 0; i < n; ++i) {
+        memcpy(blob + in_off[i], file[i], (size_t)(in_off[i + 1] - in_off[i]));
+        free(file[i]);
+    }
     if (kv_b64enc_batch(blob, in_off, n, enc, out_off) != KV_OK) {
         fprintf(stderr, "kv_b64enc_batch: %s\n", kv_last_error());
         return 1;
@@ -73,6 +77,8 @@ int main(int argc, char **argv) {
         }
         printf("  userdata: %.*s\n", (int)kv_b64enc_len((size_t)len), enc + out_off[i]);
     }
+    kv_pinned_free(blob);
+    kv_pinned_free(enc);
     kv_shutdown();
     return 0;
 }

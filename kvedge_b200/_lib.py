@@ -58,6 +58,8 @@ SIGNATURES = {
     "kv_free": (None, [C.c_void_p]),
     "kv_set_device": (C.c_int, [C.c_int]),
     "kv_shutdown": (None, []),
+    "kv_pinned_alloc": (C.c_void_p, [C.c_size_t]),
+    "kv_pinned_free": (None, [C.c_void_p]),
 }
 
 

@@ -207,3 +207,17 @@ def b64dec_device(d_in, d_in_off, d_out, d_out_off, d_out_len, d_status, d_scrat
 __all__ = ["b64enc", "b64dec", "b64enc_many", "b64dec_many", "b64enc_packed", "b64dec_packed",
            "b64enc_device", "b64enc_device_static", "b64dec_device", "b64enc_plan_device", "b64enc_run_device", "scratch_bytes", "encode_offsets", "decode_offsets",
            "encoded_len", "CorruptInputError", "KvError"]
+
+
+def pinned_empty(n: int) -> np.ndarray:
+    """``n`` bytes of page-locked host memory as a uint8 array (``kv_pinned_alloc``); buffers
+    handed to the host-buffer entry points should come from here, see include/kvedge_b200.h."""
+    import ctypes as C
+    import weakref
+    L = _lib.lib()
+    p = L.kv_pinned_alloc(max(int(n), 1))
+    if not p:
+        raise MemoryError(f"kv_pinned_alloc({n}): {L.kv_last_error().decode('utf-8', 'replace')}")
+    arr = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(max(int(n), 1),))[:int(n)]
+    weakref.finalize(arr.base if arr.base is not None else arr, L.kv_pinned_free, p)
+    return arr

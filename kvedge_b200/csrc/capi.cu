@@ -513,6 +513,26 @@ int kv_set_device(int device) {
     return KV_OK;
 }
 
+void *kv_pinned_alloc(size_t bytes) {
+    void *p = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        if (ctx_init() != KV_OK) return nullptr;
+        if (cudaSetDevice(g_ctx.device) != cudaSuccess) return nullptr;
+    }
+    cudaError_t e = cudaMallocHost(&p, bytes ? bytes : 1);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        fail(KV_ENOMEM, "cudaMallocHost(%zu): %s", bytes, cudaGetErrorString(e));
+        return nullptr;
+    }
+    return p;
+}
+
+void kv_pinned_free(void *p) {
+    if (p) (void)cudaFreeHost(p);
+}
+
 void kv_shutdown(void) {
     std::lock_guard<std::mutex> lk(g_mu);
     if (!g_ctx.ready) return;

@@ -332,3 +332,21 @@ def test_concurrent_callers_are_serialised_not_corrupted(torch_cuda):
         th.join(timeout=300)
     assert not any(th.is_alive() for th in threads), "a caller hung"
     assert not errors, errors
+
+
+def test_pinned_buffers_from_the_library(torch_cuda):
+    from kvedge_b200 import _lib
+    rng = np.random.default_rng(5)
+    units = [rng.bytes(int(s)) for s in rng.integers(0, 30000, 500)]
+    blob, in_off = workload.pack(units)
+    out_off = b64.encode_offsets(in_off, align=16)
+    h_in = b64.pinned_empty(len(blob))
+    h_in[:] = blob
+    h_out = b64.pinned_empty(int(out_off[-1]))
+    _lib.check(_lib.lib().kv_b64enc_batch(h_in.ctypes.data, in_off.ctypes.data, len(units),
+                                          h_out.ctypes.data, out_off.ctypes.data))
+    raw = h_out.tobytes()
+    for i, u in enumerate(units):
+        a = int(out_off[i])
+        assert raw[a:a + b64.encoded_len(len(u))] == ob64.encode(u), i
+    del h_in, h_out          # finalizers return the memory with kv_pinned_free
