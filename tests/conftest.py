@@ -8,8 +8,38 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 REFERENCE = "/root/reference"
-REF_CHART = os.path.join(REFERENCE, "deployment", "helm")
 GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def _materialise_reference_chart() -> str:
+    """The reference's chart (deployment/helm, eleven files) rebuilt in a temporary directory
+    from tests/golden/reference_chart_files.json, so that the same tests run in the build
+    container and on the GPU box, where /root/reference does not exist."""
+    import atexit
+    import base64
+    import hashlib
+    import json
+    import shutil
+    import tempfile
+    with open(os.path.join(GOLDEN, "reference_chart_files.json")) as f:
+        frozen = json.load(f)["files"]
+    top = tempfile.mkdtemp(prefix="kvedge_refchart_")
+    atexit.register(shutil.rmtree, top, ignore_errors=True)
+    # the chart directory keeps the reference's own base name: it is not part of any output
+    # (Helm uses Chart.yaml's name), but error messages quote it
+    root = os.path.join(top, "helm")
+    for ent in frozen:
+        raw = base64.b64decode(ent["b64"])
+        assert hashlib.sha256(raw).hexdigest() == ent["sha256"] and len(raw) == ent["len"], ent["path"]
+        dst = os.path.join(root, ent["path"])
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        with open(dst, "wb") as out:
+            out.write(raw)
+    return root
+
+
+REF_CHART = _materialise_reference_chart()
+REF_CHART_LIVE = os.path.join(REFERENCE, "deployment", "helm")
 
 
 def pytest_configure(config):
@@ -18,7 +48,7 @@ def pytest_configure(config):
 
 
 def pytest_collection_modifyitems(config, items):
-    have_ref = os.path.isdir(REF_CHART)
+    have_ref = os.path.isdir(REF_CHART_LIVE)
     for it in items:
         if "needs_reference" in it.keywords and not have_ref:
             it.add_marker(pytest.mark.skip(reason="/root/reference is not present on this machine"))
@@ -47,4 +77,12 @@ def golden_vectors():
 def golden_chart():
     import json
     with open(os.path.join(GOLDEN, "reference_chart.json")) as f:
+        return json.load(f)
+
+
+@pytest.fixture(scope="session")
+def go_tables():
+    """Go's own encoding/base64 test tables (tests/golden/go_base64_tables.json)."""
+    import json
+    with open(os.path.join(GOLDEN, "go_base64_tables.json")) as f:
         return json.load(f)

@@ -14,10 +14,17 @@ What is frozen, and where it comes from:
                             against a real Helm binary.
   * stream hashes ......... SHA-256 of the oracle's `helm template` stream for BASELINE.json
                             configs 1 and 2 (restatement-derived).
+  * reference_chart_files  the eleven files of deployment/helm (Chart.yaml, values.yaml, .helmignore,
+                            templates/*), byte for byte, base64-wrapped with their paths and
+                            SHA-256.  They are the INPUT of the path (the chart is data, not
+                            program): frozen so that tests/conftest.py can materialise the
+                            chart in a temporary directory on the GPU box, where
+                            /root/reference does not exist, and BASELINE.json configs[0] and
+                            configs[1] can run through the product path there.
   * b64_vectors ........... RFC 4648 section 10 vectors plus seeded vectors whose expected
                             outputs come from two encoders independent of this repo:
                             coreutils `base64 -w0` and CPython binascii.
-Only outputs and hashes are stored; no reference source file is copied.
+Apart from the chart's data files named above, only outputs and hashes are stored.
 """
 import hashlib
 import json
@@ -103,6 +110,19 @@ def main():
     }
     with open(os.path.join(HERE, "reference_chart.json"), "w") as f:
         json.dump(ref, f, indent=1, sort_keys=True)
+        f.write("\n")
+
+    # the chart itself, as test input for machines without /root/reference
+    files = []
+    for base, _dirs, names in sorted(os.walk(CHART)):
+        for nm in sorted(names):
+            full = os.path.join(base, nm)
+            raw = open(full, "rb").read()
+            files.append({"path": os.path.relpath(full, CHART), "sha256": sha(raw), "len": len(raw),
+                          "b64": binascii.b2a_base64(raw, newline=False).decode()})
+    with open(os.path.join(HERE, "reference_chart_files.json"), "w") as f:
+        json.dump({"source": "levi106/kvedge deployment/helm (input data of the path; see make_golden.py)",
+                   "files": files}, f, indent=1, sort_keys=True)
         f.write("\n")
 
     # base64 vectors, expected values from coreutils AND binascii (must agree)

@@ -1,5 +1,6 @@
 """GPU parity: the CUDA path, called through the C ABI, against the CPU checker (oracle/)
 and the committed golden vectors. Bit-exact: this is byte work, there is no tolerance."""
+import binascii
 import hashlib
 
 import numpy as np
@@ -115,6 +116,49 @@ def test_decode_error_offsets_match_go(torch_cuda, golden_vectors):
             with pytest.raises(b64.CorruptInputError) as ei:
                 b64.b64dec(text)
             assert ei.value.offset == c["offset"], text
+
+
+def test_go_tables_through_host_and_device_decode(torch_cuda, go_tables):
+    """Go's own encoding/base64 tables (TestDecodeCorrupt, pairs, bigtest, TestNewLineCharacters;
+    tests/golden/go_base64_tables.json -- vectors this repo's oracle did not write) through
+    kv_b64enc / kv_b64dec and, as one packed batch, through kv_b64dec_batch_dev."""
+    torch = torch_cuda
+    texts, want = [], []                     # want: bytes when accepted, int offset when corrupt
+    for p in go_tables["pairs"] + [{"decoded_hex": go_tables["bigtest"]["decoded"].encode().hex(),
+                                    "encoded": go_tables["bigtest"]["encoded"]}]:
+        raw = bytes.fromhex(p["decoded_hex"])
+        assert b64.b64enc(raw) == p["encoded"].encode()
+        texts.append(p["encoded"].encode()); want.append(raw)
+    for c in go_tables["decode_corrupt"]:
+        texts.append(c["input"].encode())
+        want.append(binascii.a2b_base64(c["input"].encode()) if c["offset"] < 0 else c["offset"])
+    for ex in go_tables["newline_characters"]["examples"]:
+        texts.append(ex.encode()); want.append(go_tables["newline_characters"]["expected"].encode())
+    for text, w in zip(texts, want):
+        if isinstance(w, bytes):
+            assert b64.b64dec(text) == w, text
+        else:
+            with pytest.raises(b64.CorruptInputError) as ei:
+                b64.b64dec(text)
+            assert ei.value.offset == w, text
+    # the same table as ONE device-resident batch, in both layouts the kernel distinguishes
+    for align in (16, 1):
+        blob, off = workload.pack(texts)
+        dec_off = b64.decode_offsets(off, align=align)
+        d_in = torch.from_numpy(blob).cuda()
+        d_out = torch.zeros(int(dec_off[-1]) + 16, dtype=torch.uint8, device="cuda")
+        d_len = torch.zeros(len(texts), dtype=torch.int64, device="cuda")
+        d_status = torch.zeros(len(texts), dtype=torch.int64, device="cuda")
+        scratch = torch.empty(b64.scratch_bytes(len(texts), len(blob)), dtype=torch.uint8, device="cuda")
+        b64.b64dec_device(d_in, torch.from_numpy(off).cuda(), d_out, torch.from_numpy(dec_off).cuda(),
+                          d_len, d_status, scratch)
+        torch.cuda.synchronize()
+        out, lens, status = d_out.cpu().numpy().tobytes(), d_len.cpu().numpy(), d_status.cpu().numpy()
+        for i, (text, w) in enumerate(zip(texts, want)):
+            if isinstance(w, bytes):
+                assert status[i] == -1 and out[int(dec_off[i]):int(dec_off[i]) + int(lens[i])] == w, (align, text)
+            else:
+                assert status[i] == w, (align, text)
 
 
 def test_decode_batch_mixed_clean_and_corrupt(torch_cuda):

@@ -120,7 +120,6 @@ def test_property_engines_agree_on_random_overrides(name, payload):
 
 
 # ---- the reference chart itself (build container only) -------------------------------------
-@pytest.mark.needs_reference
 def test_reference_chart_config1_matches_oracle_and_golden(golden_chart):
     r = _plan_and_fill(REF_CHART)
     m = r.manifest()
@@ -131,7 +130,6 @@ def test_reference_chart_config1_matches_oracle_and_golden(golden_chart):
     assert helm.lint(REF_CHART) == (golden_chart["lint"]["ok"], golden_chart["lint"]["messages"])
 
 
-@pytest.mark.needs_reference
 def test_reference_chart_config2_matches_golden(golden_chart, tmp_path):
     g = golden_chart["config2"]
     cfg = workload.config_toml(g["config_toml_seed"])
@@ -145,13 +143,11 @@ def test_reference_chart_config2_matches_golden(golden_chart, tmp_path):
     assert r.pending[1].endswith(b"sudo iotedge config apply")
 
 
-@pytest.mark.needs_reference
 def test_reference_notes_equal_cast2294(golden_chart):
     r = _plan_and_fill(REF_CHART, golden_chart["release_name_cast2294"], set=["nameOverride=aziot-edge-kubevirt"])
     assert r.notes().decode() == golden_chart["notes_cast2294"]
 
 
-@pytest.mark.needs_reference
 def test_reference_name_helper_edge_cases():
     for override in ["a" * 39 + "-bcdef", "", "x-", "-" * 45, "é" * 25]:
         sets = [f"nameOverride={override}"]

@@ -115,3 +115,48 @@ def test_survey_fingerprints_of_default_cloudinit_payload(golden_chart):
     assert payload.startswith(b"#cloud-config\nhostname: iotedgevm\n")
     assert payload.endswith(b"sudo iotedge config apply")
     assert ob64.encode(payload) == b64_text
+
+
+# ---- pin (vi): Go's own encoding/base64 test tables (not produced by this repo's oracle) --------
+def _coreutils_decode(text: bytes):
+    """coreutils `base64 -d`: (ok, bytes).  It skips '\\n' on its own; '\\r' needs -i, which would
+    also hide garbage, so texts with '\\r' are not sent here."""
+    res = subprocess.run(["base64", "-d"], input=text, capture_output=True)
+    return res.returncode == 0, res.stdout
+
+
+def test_go_pairs_and_bigtest(go_tables):
+    rows = [(bytes.fromhex(p["decoded_hex"]), p["encoded"].encode()) for p in go_tables["pairs"]]
+    rows.append((go_tables["bigtest"]["decoded"].encode(), go_tables["bigtest"]["encoded"].encode()))
+    for raw, enc in rows:
+        assert ob64.encode(raw) == enc
+        assert ob64.decode(enc) == raw
+        assert ob64.encoded_len(len(raw)) == len(enc)
+
+
+def test_go_decode_corrupt_table(go_tables):
+    """TestDecodeCorrupt: Go's published input -> CorruptInputError offset pairs (-1 = accepted).
+    The consumer side of the path (aziot-edge-vm.yaml:49-51, _helper.tpl:64,73) decodes with
+    exactly these semantics."""
+    assert len(go_tables["decode_corrupt"]) == 24
+    for c in go_tables["decode_corrupt"]:
+        text = c["input"].encode()
+        if c["offset"] < 0:
+            out = ob64.decode(text)
+            assert out == binascii.a2b_base64(text), text
+            if shutil.which("base64") and b"\r" not in text:
+                assert _coreutils_decode(text) == (True, out), text
+        else:
+            with pytest.raises(ob64.CorruptInputError) as ei:
+                ob64.decode(text)
+            assert ei.value.offset == c["offset"], text
+
+
+def test_go_newline_characters(go_tables):
+    want = go_tables["newline_characters"]["expected"].encode()
+    for ex in go_tables["newline_characters"]["examples"]:
+        text = ex.encode()
+        assert ob64.decode(text) == want, text
+        assert binascii.a2b_base64(text) == want
+        if shutil.which("base64") and b"\r" not in text:
+            assert _coreutils_decode(text) == (True, want), text

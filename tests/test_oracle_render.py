@@ -2,9 +2,9 @@
 
 * cast:2294 of the reference's own asciinema recording holds the only real-Helm output in
   the repo (the NOTES block); the golden copy is in tests/golden/reference_chart.json.
-* Tests marked needs_reference re-render from /root/reference and therefore only run in
-  the build container; the hash goldens they produce are compared on every machine by the
-  C++ engine tests.
+* The chart itself is materialised from tests/golden/reference_chart_files.json (conftest.py),
+  so every render test runs on every machine; the two tests marked needs_reference check the
+  frozen copies (chart files, cast line) against /root/reference in the build container.
 """
 import hashlib
 import json
@@ -17,23 +17,41 @@ from kvedge_b200 import workload
 from oracle import b64 as ob64
 from oracle import gotmpl, helmref
 
-from conftest import REF_CHART, REFERENCE
+from conftest import GOLDEN, REF_CHART, REF_CHART_LIVE, REFERENCE
 
 CAST = os.path.join(REFERENCE, "deployment", "az-iot-edge-k8s-kubevirt-ascii.cast")
 
 
 @pytest.mark.needs_reference
-def test_notes_equals_real_helm_output_cast2294(golden_chart):
+def test_golden_notes_are_the_casts_text(golden_chart):
     with open(CAST) as f:
         ev = json.loads(f.read().splitlines()[2293])
     recorded = ev[2].replace("\r\n", "\n").split("NOTES:\n", 1)[1].strip()
     assert recorded == golden_chart["notes_cast2294"]  # the committed golden is the cast's text
+
+
+@pytest.mark.needs_reference
+def test_frozen_chart_files_are_the_references_bytes():
+    with open(os.path.join(GOLDEN, "reference_chart_files.json")) as f:
+        frozen = {e["path"]: e for e in json.load(f)["files"]}
+    live = {}
+    for base, _d, names in os.walk(REF_CHART_LIVE):
+        for nm in names:
+            full = os.path.join(base, nm)
+            live[os.path.relpath(full, REF_CHART_LIVE)] = open(full, "rb").read()
+    assert sorted(frozen) == sorted(live) and len(live) == 11
+    for path, raw in live.items():
+        assert hashlib.sha256(raw).hexdigest() == frozen[path]["sha256"], path
+        assert open(os.path.join(REF_CHART, path), "rb").read() == raw, path
+
+
+def test_notes_equals_real_helm_output_cast2294(golden_chart):
+    recorded = golden_chart["notes_cast2294"]
     notes = helmref.helm_notes(REF_CHART, golden_chart["release_name_cast2294"],
                                set_args=["nameOverride=aziot-edge-kubevirt"])
     assert notes.decode() == recorded
 
 
-@pytest.mark.needs_reference
 def test_object_names_seen_in_cast(golden_chart):
     stream = helmref.helm_template(REF_CHART).decode()
     assert "name: aziot-edge-kubevirt-linux-dv\n" in stream
@@ -42,7 +60,6 @@ def test_object_names_seen_in_cast(golden_chart):
     assert "aziot-edge-kubevirt-linux" in golden_chart["cast_object_lines"]["cast:2579"]
 
 
-@pytest.mark.needs_reference
 def test_config1_stream_matches_golden(golden_chart):
     s = helmref.helm_template(REF_CHART)
     g = golden_chart["config1"]
@@ -52,7 +69,6 @@ def test_config1_stream_matches_golden(golden_chart):
     assert helmref.secret_userdata(s, "aziot-edge-kubevirt-vm-aziotedgeconfig") == b""
 
 
-@pytest.mark.needs_reference
 def test_config2_secret_is_byte_exact(golden_chart, tmp_path):
     """BASELINE.json config 2: helm template --set-file azIotEdgeConfig=config.toml."""
     g = golden_chart["config2"]
@@ -70,7 +86,6 @@ def test_config2_secret_is_byte_exact(golden_chart, tmp_path):
     assert b"\n  - " + workload.ssh_key(g["ssh_key_seed"]) + b"\napt:" in ci   # _helper.tpl:35
 
 
-@pytest.mark.needs_reference
 def test_helmignore_drops_http_disk_datavolume():
     chart = helmref.load_chart(REF_CHART)
     assert "templates/aziot-edge-data-volume-disk.yaml" not in chart.templates   # .helmignore:25
@@ -78,7 +93,6 @@ def test_helmignore_drops_http_disk_datavolume():
     assert helmref.helm_template(REF_CHART).count(b"kind: DataVolume") == 1
 
 
-@pytest.mark.needs_reference
 def test_manifest_order_and_framing():
     s = helmref.helm_template(REF_CHART).decode()
     srcs = re.findall(r"(?m)^# Source: (.*)$", s)
@@ -92,7 +106,6 @@ def test_manifest_order_and_framing():
     assert "# TODO: we should be using aziot-edge-kubevirt here instead" in s
 
 
-@pytest.mark.needs_reference
 def test_service_toggle_and_eq_type_error():
     off = helmref.helm_template(REF_CHART, set_args=["aziotEdgeVmEnableExternalSsh=false"])
     assert b"kind: Service" not in off
@@ -100,7 +113,6 @@ def test_service_toggle_and_eq_type_error():
         helmref.helm_template(REF_CHART, set_string_args=["aziotEdgeVmEnableExternalSsh=true"])
 
 
-@pytest.mark.needs_reference
 def test_name_helper_vs_raw_name_override():
     long = "a" * 39 + "-bcdef"
     s = helmref.helm_template(REF_CHART, set_args=[f"nameOverride={long}"]).decode()
@@ -111,7 +123,6 @@ def test_name_helper_vs_raw_name_override():
     assert "\n  name: -vm-cloudconfig" in s
 
 
-@pytest.mark.needs_reference
 def test_lint_passes_with_icon_info(golden_chart):
     ok, msgs = helmref.helm_lint(REF_CHART)
     assert ok and msgs == ["[INFO] Chart.yaml: icon is recommended"]

@@ -43,7 +43,6 @@ def test_fixture_secret_round_trips_to_the_input_file(name):
     assert b"\n" not in ud and b" " not in ud and len(ud) == (len(raw) + 2) // 3 * 4
 
 
-@pytest.mark.needs_reference
 def test_reference_consumer_side_round_trip_and_cross_references(tmp_path):
     cfg = workload.config_toml(0, crlf=True)          # CRLF file: must survive byte for byte
     p = tmp_path / "config.toml"
@@ -65,7 +64,6 @@ def test_reference_consumer_side_round_trip_and_cross_references(tmp_path):
     assert f"grep {serial} " in ci and "cp /mnt/app-secret/userdata /etc/aziot/config.toml" in ci
 
 
-@pytest.mark.needs_reference
 def test_reference_cloud_config_is_sane_yaml():
     key = workload.ssh_key(0).decode()
     stream = _render(REF_CHART, set=[f"publicSshKey={key}"])
