@@ -600,6 +600,31 @@ void apply_set_blob(Value &values, const std::string &key, std::string content) 
     assign(values, split_key(key), v);
 }
 
+// ============================================================================ coalesce
+namespace {
+
+// chartutil.coalesceTablesFullKey: dst = the user's table, src = the chart's.
+void coalesce_tables(tmpl::Map &dst, const tmpl::Map &src) {
+    for (const auto &kv : src) {
+        auto it = dst.find(kv.first);
+        if (it == dst.end()) {
+            dst[kv.first] = tmpl::deep_copy(kv.second);
+        } else if (it->second.kind == Value::Nil) {
+            dst.erase(it);                                  // "when the YAML value is null, we remove it"
+        } else if (kv.second.kind == Value::MapK && it->second.kind == Value::MapK) {
+            coalesce_tables(*it->second.map, *kv.second.map);
+        }                                                   // otherwise the user's value stands (Helm warns)
+    }
+}
+
+}  // namespace
+
+Value coalesce_values(const Value &defaults, Value user) {
+    if (user.kind != Value::MapK) user = Value::make_map();
+    if (defaults.kind == Value::MapK) coalesce_tables(*user.map, *defaults.map);
+    return user;
+}
+
 // ============================================================================ chart
 namespace {
 

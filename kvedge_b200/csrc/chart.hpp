@@ -24,6 +24,12 @@ void apply_set(Value &values, const std::string &expr, bool force_string);
 void apply_set_file(Value &values, const std::string &expr);                 // key=path
 void apply_set_blob(Value &values, const std::string &key, std::string content);
 
+// pkg/chartutil CoalesceValues: the chart's defaults slide UNDER the user's values (--set and
+// friends, collected into a map of their own first).  A user value of null deletes the key
+// when the chart has a default for it; tables merge key by key; lists and scalars of the user
+// win whole (`--set ports[0].port=1` replaces the chart's list, it does not patch it).
+Value coalesce_values(const Value &defaults, Value user);
+
 struct Chart {
     std::string dir;
     Value metadata;                                // Chart.yaml as a map

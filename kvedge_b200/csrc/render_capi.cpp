@@ -116,15 +116,17 @@ std::string gpu_decode_one(const std::string &in) {
 }
 
 Value merged_values(const kv_chart *c, const kv_overrides *ov) {
-    Value vals = kvedge::tmpl::deep_copy(c->chart.values);
-    if (!ov) return vals;
+    if (!ov) return kvedge::tmpl::deep_copy(c->chart.values);
+    // Helm collects the flags into a map of their own and then slides the chart's defaults
+    // under it (chartutil.CoalesceValues): null deletes a default, lists are not patched.
+    Value vals = Value::make_map();
     for (int i = 0; i < ov->n_set; ++i) kvedge::chart::apply_set(vals, ov->set[i], false);
     for (int i = 0; i < ov->n_set_string; ++i) kvedge::chart::apply_set(vals, ov->set_string[i], true);
     for (int i = 0; i < ov->n_set_file; ++i) kvedge::chart::apply_set_file(vals, ov->set_file[i]);
     for (int i = 0; i < ov->n_blob; ++i)
         kvedge::chart::apply_set_blob(vals, ov->blob_keys[i],
                                       std::string(reinterpret_cast<const char *>(ov->blob_data[i]), ov->blob_len[i]));
-    return vals;
+    return kvedge::chart::coalesce_values(c->chart.values, std::move(vals));
 }
 
 // Render every non-partial file of the chart; keys are "<chart>/templates/<file>".

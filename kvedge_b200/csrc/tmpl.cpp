@@ -810,6 +810,17 @@ std::string go_typename(const Value &v) {
     return k;
 }
 
+// An argument bound to a Go `string` parameter (Sprig's b64enc, trunc, indent, ... are plain
+// func(string) string): text/template refuses anything else instead of printing it --
+// "wrong type for value; expected string; got int64", and for nil / a missing key
+// "invalid value; expected string" -- so `--set azIotEdgeConfig=12345` aborts the render
+// rather than encoding "12345" (aziot-edge-runtime-config-secret.yaml:6).
+const std::string &string_arg(const Value &v, const std::string &fn) {
+    if (v.kind == Value::String) return v.s;
+    if (v.is_nilish()) throw Error("executing at <" + fn + ">: invalid value; expected string");
+    throw Error("executing at <" + fn + ">: wrong type for value; expected string; got " + go_typename(v));
+}
+
 std::string sprintf_fn(const std::vector<Value> &a) {
     if (a.empty()) throw Error("wrong number of args for printf: want at least 1 got 0");
     std::string fmt = strval(a[0]), o;
@@ -923,25 +934,25 @@ struct Exec {
         if (fn == "trunc") {
             need(2);
             int64_t c = to_int(a[0]);
-            std::string s = strval(a[1]);
+            std::string s = string_arg(a[1], fn);
             if (c < 0 && (int64_t)s.size() + c > 0) return Value::str(s.substr((size_t)((int64_t)s.size() + c)));
             if (c >= 0 && (int64_t)s.size() > c) return Value::str(s.substr(0, (size_t)c));
             return Value::str(s);
         }
         if (fn == "trimSuffix") {
             need(2);
-            std::string suf = strval(a[0]), s = strval(a[1]);
+            std::string suf = string_arg(a[0], fn), s = string_arg(a[1], fn);
             if (!suf.empty() && s.size() >= suf.size() && s.compare(s.size() - suf.size(), suf.size(), suf) == 0)
                 s.erase(s.size() - suf.size());
             return Value::str(s);
         }
         if (fn == "trimPrefix") {
             need(2);
-            std::string pre = strval(a[0]), s = strval(a[1]);
+            std::string pre = string_arg(a[0], fn), s = string_arg(a[1], fn);
             if (!pre.empty() && s.compare(0, pre.size(), pre) == 0) s.erase(0, pre.size());
             return Value::str(s);
         }
-        if (fn == "replace") { need(3); return Value::str(replace_all(strval(a[2]), strval(a[0]), strval(a[1]))); }
+        if (fn == "replace") { need(3); return Value::str(replace_all(string_arg(a[2], fn), string_arg(a[0], fn), string_arg(a[1], fn))); }
         if (fn == "quote" || fn == "squote") {
             std::string o;
             bool first = true;
@@ -956,14 +967,14 @@ struct Exec {
         if (fn == "indent" || fn == "nindent") {
             need(2);
             std::string pad((size_t)std::max<int64_t>(0, to_int(a[0])), ' ');
-            std::string o = pad + replace_all(strval(a[1]), "\n", "\n" + pad);
+            std::string o = pad + replace_all(string_arg(a[1], fn), "\n", "\n" + pad);
             return Value::str(fn == "nindent" ? "\n" + o : o);
         }
-        if (fn == "b64enc") { need(1); return Value::str(encode_now(strval(a[0]))); }
+        if (fn == "b64enc") { need(1); return Value::str(encode_now(string_arg(a[0], fn))); }
         if (fn == "b64dec") {
             need(1);
             if (!opt.decode) throw Error("b64dec: no decoder attached (GPU required)");
-            return Value::str(opt.decode(strval(a[0])));
+            return Value::str(opt.decode(string_arg(a[0], fn)));
         }
         if (fn == "eq") return Value::boolean(eq_fn(a));
         if (fn == "ne") { need(2); return Value::boolean(!eq_fn(a)); }
@@ -998,11 +1009,11 @@ struct Exec {
             if (a[1].is_nilish() || (a[1].kind == Value::String && a[1].s.empty())) throw Error(strval(a[0]));
             return a[1];
         }
-        if (fn == "lower") { need(1); return Value::str(ascii_map(strval(a[0]), ::tolower)); }
-        if (fn == "upper") { need(1); return Value::str(ascii_map(strval(a[0]), ::toupper)); }
+        if (fn == "lower") { need(1); return Value::str(ascii_map(string_arg(a[0], fn), ::tolower)); }
+        if (fn == "upper") { need(1); return Value::str(ascii_map(string_arg(a[0], fn), ::toupper)); }
         if (fn == "trim") {
             need(1);
-            std::string s = strval(a[0]);
+            std::string s = string_arg(a[0], fn);
             size_t x = 0, y = s.size();
             while (x < y && (is_space(s[x]) || s[x] == '\v' || s[x] == '\f')) ++x;
             while (y > x && (is_space(s[y - 1]) || s[y - 1] == '\v' || s[y - 1] == '\f')) --y;
@@ -1025,16 +1036,16 @@ struct Exec {
             }
             return Value::str(o);
         }
-        if (fn == "contains") { need(2); return Value::boolean(strval(a[1]).find(strval(a[0])) != std::string::npos); }
-        if (fn == "hasPrefix") { need(2); std::string p = strval(a[0]), s = strval(a[1]); return Value::boolean(s.compare(0, p.size(), p) == 0); }
+        if (fn == "contains") { need(2); return Value::boolean(string_arg(a[1], fn).find(string_arg(a[0], fn)) != std::string::npos); }
+        if (fn == "hasPrefix") { need(2); std::string p = string_arg(a[0], fn), s = string_arg(a[1], fn); return Value::boolean(s.compare(0, p.size(), p) == 0); }
         if (fn == "hasSuffix") {
             need(2);
-            std::string p = strval(a[0]), s = strval(a[1]);
+            std::string p = string_arg(a[0], fn), s = string_arg(a[1], fn);
             return Value::boolean(s.size() >= p.size() && s.compare(s.size() - p.size(), p.size(), p) == 0);
         }
         if (fn == "repeat") {
             need(2);
-            std::string o, s = strval(a[1]);
+            std::string o, s = string_arg(a[1], fn);
             for (int64_t k = 0; k < to_int(a[0]); ++k) o += s;
             return Value::str(o);
         }
@@ -1119,7 +1130,8 @@ struct Exec {
             return false;
         if (opt.pending->size() >= TemplateSet::kMaxPending) return false;
         Value in = eval_pipe_prefix(p, p.cmds.size() - 1, dot, sc);
-        std::string s = in.kind == Value::String ? std::move(in.s) : strval(in);   // a config.toml: do not copy it again
+        string_arg(in, "b64enc");                // same refusal as the immediate path
+        std::string s = std::move(in.s);         // a config.toml: do not copy it again
         if (s.empty()) return true;  // b64enc "" == ""
         Pending pd;
         pd.encoded_len = (s.size() + 2) / 3 * 4;

@@ -142,6 +142,21 @@ def strval(v: Any) -> bytes:
     return go_print(v)
 
 
+def string_arg(v: Any) -> bytes:
+    """An argument bound to a Go ``string`` parameter.  text/template's validateType refuses
+    anything that is not a string (``wrong type for value; expected string; got int64``;
+    for nil or a missing key ``invalid value; expected string``): Sprig's b64enc, trunc,
+    indent, trimSuffix, replace ... are plain ``func(string) string``.  Reference sites:
+    aziot-edge-runtime-config-secret.yaml:6 (``--set azIotEdgeConfig=12345`` aborts in Helm)."""
+    if isinstance(v, bytes):
+        return v
+    if isinstance(v, str):
+        return v.encode("utf-8")
+    if v is None or v is NOVALUE:
+        raise TemplateError("invalid value; expected string")
+    raise TemplateError("wrong type for value; expected string; got " + _go_typename(v).decode())
+
+
 def go_quote(s: bytes) -> bytes:
     """``strconv.Quote``: double-quoted Go string literal of ``s``."""
     out = bytearray(b'"')
@@ -785,7 +800,7 @@ def _toint(v: Any) -> int:
 def _trunc(c: Any, s: Any) -> bytes:
     """Sprig ``trunc`` (reference: _helper.tpl:7,14). Slices BYTES, as Go does."""
     c = _toint(c)
-    s = strval(s)
+    s = string_arg(s)
     if c < 0 and len(s) + c > 0:
         return s[len(s) + c:]
     if c >= 0 and len(s) > c:
@@ -795,14 +810,14 @@ def _trunc(c: Any, s: Any) -> bytes:
 
 def _trim_suffix(suffix: Any, s: Any) -> bytes:
     """Sprig ``trimSuffix`` = strings.TrimSuffix(s, suffix) (reference: _helper.tpl:7,14)."""
-    suffix, s = strval(suffix), strval(s)
+    suffix, s = string_arg(suffix), string_arg(s)
     if suffix and s.endswith(suffix):
         return s[:len(s) - len(suffix)]
     return s
 
 
 def _trim_prefix(prefix: Any, s: Any) -> bytes:
-    prefix, s = strval(prefix), strval(s)
+    prefix, s = string_arg(prefix), string_arg(s)
     if prefix and s.startswith(prefix):
         return s[len(prefix):]
     return s
@@ -810,7 +825,7 @@ def _trim_prefix(prefix: Any, s: Any) -> bytes:
 
 def _replace(old: Any, new: Any, src: Any) -> bytes:
     """Sprig ``replace`` = strings.Replace(src, old, new, -1) (reference: _helper.tpl:14)."""
-    old, new, src = strval(old), strval(new), strval(src)
+    old, new, src = string_arg(old), string_arg(new), string_arg(src)
     if old == b"":
         # Go inserts `new` before every rune and at the end
         runes = src.decode("utf-8", errors="surrogateescape")
@@ -832,7 +847,7 @@ def _indent(n: Any, s: Any) -> bytes:
     """Sprig ``indent`` (reference: aziot-edge-vm.yaml:13 and three more sites):
     pad + strings.Replace(s, "\\n", "\\n"+pad, -1)."""
     pad = b" " * _toint(n)
-    return pad + strval(s).replace(b"\n", b"\n" + pad)
+    return pad + string_arg(s).replace(b"\n", b"\n" + pad)
 
 
 def _nindent(n: Any, s: Any) -> bytes:
@@ -842,13 +857,13 @@ def _nindent(n: Any, s: Any) -> bytes:
 def _b64enc(s: Any) -> bytes:
     """Sprig ``b64enc`` (reference: aziot-edge-runtime-config-secret.yaml:6,
     aziot-edge-vm-cloud-init-secret.yaml:6)."""
-    return _b64.encode(strval(s))
+    return _b64.encode(string_arg(s))
 
 
 def _b64dec(s: Any) -> bytes:
     """Sprig ``b64dec``: on error returns the error text, as Sprig does."""
     try:
-        return _b64.decode(strval(s))
+        return _b64.decode(string_arg(s))
     except _b64.CorruptInputError as e:
         return str(e).encode()
 
@@ -998,16 +1013,16 @@ BUILTINS: Dict[str, Callable] = {
     "len": _len,
     "empty": _is_empty,
     "required": _required,
-    "lower": lambda s: strval(s).decode("utf-8", "surrogateescape").lower().encode("utf-8", "surrogateescape"),
-    "upper": lambda s: strval(s).decode("utf-8", "surrogateescape").upper().encode("utf-8", "surrogateescape"),
-    "trim": lambda s: strval(s).decode("utf-8", "surrogateescape").strip().encode("utf-8", "surrogateescape"),
+    "lower": lambda s: string_arg(s).decode("utf-8", "surrogateescape").lower().encode("utf-8", "surrogateescape"),
+    "upper": lambda s: string_arg(s).decode("utf-8", "surrogateescape").upper().encode("utf-8", "surrogateescape"),
+    "trim": lambda s: string_arg(s).decode("utf-8", "surrogateescape").strip().encode("utf-8", "surrogateescape"),
     "toString": lambda v: strval(v),
     "hasKey": lambda d, k: (strval(k) in d) or (strval(k).decode() in d),
     "ternary": lambda t, f, c: t if is_true(c) else f,
     "cat": lambda *a: b" ".join(strval(x) for x in a if x is not None and x is not NOVALUE),
-    "contains": lambda sub, s: strval(sub) in strval(s),
-    "hasPrefix": lambda p, s: strval(s).startswith(strval(p)),
-    "hasSuffix": lambda p, s: strval(s).endswith(strval(p)),
-    "repeat": lambda n, s: strval(s) * _toint(n),
-    "sha256sum": lambda s: __import__("hashlib").sha256(strval(s)).hexdigest().encode(),
+    "contains": lambda sub, s: string_arg(sub) in string_arg(s),
+    "hasPrefix": lambda p, s: string_arg(s).startswith(string_arg(p)),
+    "hasSuffix": lambda p, s: string_arg(s).endswith(string_arg(p)),
+    "repeat": lambda n, s: string_arg(s) * _toint(n),
+    "sha256sum": lambda s: __import__("hashlib").sha256(string_arg(s)).hexdigest().encode(),
 }

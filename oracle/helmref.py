@@ -353,16 +353,32 @@ DEFAULT_RELEASE = "release-name"
 def render_values(chart: Chart, set_args=(), set_string_args=(), set_file_args=(),
                   values_override: Optional[Dict[bytes, Any]] = None) -> Dict[bytes, Any]:
     import copy
-    vals = copy.deepcopy(chart.values)
+    # Helm: the flags build a map of their own (pkg/cli/values MergeValues), then
+    # chartutil.CoalesceValues slides the chart's defaults under it.
+    user: Dict[bytes, Any] = {}
     if values_override:
-        deep_merge(vals, copy.deepcopy(values_override))
+        deep_merge(user, copy.deepcopy(values_override))
     for e in set_args:
-        apply_set(vals, e)
+        apply_set(user, e)
     for e in set_string_args:
-        apply_set(vals, e, force_string=True)
+        apply_set(user, e, force_string=True)
     for e in set_file_args:
-        apply_set_file(vals, e)
-    return vals
+        apply_set_file(user, e)
+    return coalesce_values(chart.values, user)
+
+
+def coalesce_values(defaults: Dict[bytes, Any], user: Dict[bytes, Any]) -> Dict[bytes, Any]:
+    """chartutil.coalesceValues / coalesceTablesFullKey: a user null deletes a key the chart
+    defines; tables merge key by key; the user's lists and scalars win whole."""
+    import copy
+    for k, dv in defaults.items():
+        if k not in user:
+            user[k] = copy.deepcopy(dv)
+        elif user[k] is None:
+            del user[k]
+        elif isinstance(dv, dict) and isinstance(user[k], dict):
+            coalesce_values(dv, user[k])
+    return user
 
 
 def render_files(chart: Chart, values: Dict[bytes, Any], release_name: str = DEFAULT_RELEASE,

@@ -107,12 +107,20 @@ def test_lint_fixture_and_broken_chart(tmp_path):
 def test_property_engines_agree_on_random_overrides(name, payload):
     payload = bytes(c for c in payload if c != 1 and not (0x10 <= c < 0x20))
     sets = [f"nameOverride={name}"]
-    r = helm.Chart(FIXTURE).plan("p", set=sets, blobs={"sshKey": payload})
     # oracle side: inject the same blob through its values API
     ch = helmref.load_chart(FIXTURE)
     vals = helmref.render_values(ch, sets)
     helmref._assign(vals, ["sshKey"], payload)
-    ms, _ = helmref.split_manifests(helmref.render_files(ch, vals, "p"))
+    try:
+        files = helmref.render_files(ch, vals, "p")
+    except helmref.TemplateError as e:
+        # `--set nameOverride=1` is an int64 and `true` a bool: `| trunc 24` refuses them in Helm
+        assert "expected string" in str(e)
+        with pytest.raises(helm.TemplateError, match="expected string"):
+            helm.Chart(FIXTURE).plan("p", set=sets, blobs={"sshKey": payload})
+        return
+    r = helm.Chart(FIXTURE).plan("p", set=sets, blobs={"sshKey": payload})
+    ms, _ = helmref.split_manifests(files)
     ref = b"".join(b"---\n# Source: " + m.name.encode() + b"\n" + m.content + b"\n" for m in ms)
     for i, p in enumerate(r.pending):
         r.fill(i, ob64.encode(p))
@@ -179,3 +187,44 @@ def test_placeholder_byte_anywhere_in_a_value_disables_deferral(byte):
         payload = bytes([ok]) * 24
         r = helm.Chart(FIXTURE).plan("rel", blobs={"runtimeConfig": payload})
         assert payload in r.pending, ok
+
+
+# ---- string-typed Sprig functions refuse non-strings; null deletes a chart default ----------
+@pytest.mark.parametrize("flag,needle", [
+    ("azIotEdgeConfig=12345", "wrong type for value; expected string; got int"),
+    ("azIotEdgeConfig=true", "wrong type for value; expected string; got bool"),
+])
+def test_b64enc_of_a_non_string_aborts_like_helm(flag, needle):
+    """Sprig's b64enc is func(string) string: text/template aborts the render instead of
+    encoding the printed form (aziot-edge-runtime-config-secret.yaml:6)."""
+    with pytest.raises(helm.TemplateError, match=needle):
+        helm.Chart(REF_CHART).plan(set=[flag])
+    with pytest.raises(helmref.TemplateError, match=needle):
+        helmref.helm_template(REF_CHART, set_args=[flag])
+    # --set-string keeps it a string: renders, and the pending site holds the digits
+    r = helm.Chart(REF_CHART).plan(set_string=[flag])
+    assert r.pending[0] == flag.split("=", 1)[1].encode()
+
+
+def test_null_override_deletes_the_charts_default():
+    """chartutil.CoalesceValues: `--set key=null` removes a key the chart defines."""
+    # nameOverride gone: the raw reference at aziot-edge-vm-cloud-init-secret.yaml:4 prints nothing
+    sets = ["nameOverride=null"]
+    r = _plan_and_fill(REF_CHART, set=sets)
+    assert r.manifest() == helmref.helm_template(REF_CHART, set_args=sets)
+    assert b"  name: -vm-cloudconfig  \n" in r.manifest()
+    assert b"<nil>" not in r.manifest() and b"<no value>" not in r.manifest()
+    # azIotEdgeConfig gone: b64enc receives no value and the render aborts
+    with pytest.raises(helm.TemplateError, match="invalid value; expected string"):
+        helm.Chart(REF_CHART).plan(set=["azIotEdgeConfig=null"])
+    with pytest.raises(helmref.TemplateError, match="invalid value; expected string"):
+        helmref.helm_template(REF_CHART, set_args=["azIotEdgeConfig=null"])
+
+
+def test_user_lists_replace_chart_lists_and_tables_merge():
+    sets = ["ports[0].port=2222,extraLabels.team=iot,extraLabels.zone=null"]
+    r = _plan_and_fill(FIXTURE, "rel6", set=sets)
+    m = r.manifest()
+    assert m == helmref.helm_template(FIXTURE, "rel6", set_args=sets)
+    assert b"9100" not in m and b"2222" in m          # the list was replaced, not patched
+    assert b'team: "iot"' in m and b'tier: "edge"' in m and b"zone:" not in m
