@@ -88,12 +88,18 @@ int kv_b64enc_run_dev(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_un
  * ever handed input and output pointers.  For them the tile table lives in a fixed array of
  * KV_STATIC_SCRATCH_BYTES inside the library's device image; this entry point allocates
  * nothing, on the host or on the device.
- *  - Limit: the batch's tile table (kv_b64_scratch_bytes(n_units, total_in_bytes): about 32
- *    bytes per unit plus 32 bytes per 12 KiB of input) must fit in KV_STATIC_SCRATCH_BYTES;
- *    larger batches are refused with KV_ENOMEM and a message saying so.  Every GPU that
- *    loads the library holds the array until the process exits.
- *  - The first call on each device looks the array's device address up (once, with that
- *    device current); make that first call outside any stream capture.
+ *  - Limit: the batch's tile table must fit in KV_STATIC_SCRATCH_BYTES, that is
+ *        512 + 256 * ceil(ceil(n_units / 1024) / 64) + 32 * (n_units + total_in_bytes / 12288)
+ *    bytes (32 bytes per unit plus 32 bytes per 12 KiB of input, in practice; a little less
+ *    than kv_b64_scratch_bytes() reports, which is sized for decode as well).  Larger batches
+ *    are refused with KV_ENOMEM and a message saying so.  Every GPU that loads the library
+ *    holds the array until the process exits.
+ *  - The first call on each device looks the array's device address up and does the encode
+ *    kernels' one-time launch set-up (once, with that device current).  The driver loads this
+ *    library's device code and the array itself at that moment, which takes device memory
+ *    even though the library allocates none: make that first call at start-up -- before
+ *    another pool claims the remaining memory, and outside any stream capture.  A batch of
+ *    one empty unit is enough.
  *  - All calls on one GPU share the array, which keeps whatever the previous call left in
  *    it (each call rewrites everything it reads).  Two calls whose kernels overlap on the
  *    same GPU -- different streams, different threads -- race on it: serialise them.
@@ -102,6 +108,15 @@ int kv_b64enc_run_dev(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_un
 int kv_b64enc_batch_dev_static(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
                                int64_t total_in_bytes, char *d_out, const int64_t *d_out_off,
                                void *stream);
+
+/* The *_dev entries are asynchronous and read the offsets only on the device, so they cannot
+ * tell at call time whether total_in_bytes was at least d_in_off[n_units].  If it was smaller,
+ * the tile table is clamped to the size it was given: memory stays intact, but units past the
+ * clamp are NOT processed and the call has long returned KV_OK.  This entry reports it: it waits
+ * for `stream`, reads the plan's verdict out of d_scratch and returns KV_EINVAL when the last
+ * batch planned there was truncated.  (No counterpart in the reference.  The static entry keeps
+ * its table to itself and cannot be asked: give it a correct total_in_bytes.)                 */
+int kv_b64_batch_status_dev(const void *d_scratch, void *stream);
 
 /* Inverse of the above: what the Kubernetes API server / KubeVirt do to
  * Secret.data.userdata before exposing it as the `userdata` file consumed at
@@ -191,6 +206,13 @@ void kv_free(void *p);
 int kv_set_device(int device);
 /* Release the per-device staging buffers and streams held by the host-buffer path. */
 void kv_shutdown(void);
+
+/* Shape of the host-buffer pipeline (no counterpart in the reference): kv_b64enc_batch and
+ * kv_b64dec_batch cut a batch into chunks of about chunk_bytes input bytes (default 16 MiB) and
+ * keep `slots` of them in flight (default 4, at most 8), each slot owning device buffers of one
+ * chunk.  0 leaves a setting as it is.  Takes effect from the next batch; results do not depend
+ * on it, only speed and device-memory use do.                                                */
+int kv_host_pipeline_config(int64_t chunk_bytes, int slots);
 
 /* Page-locked host memory for the buffers handed to kv_b64enc_batch / kv_b64dec_batch.  (No
  * counterpart in the reference.)  The host-buffer entries accept any memory, but from ordinary

@@ -10,6 +10,7 @@ import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libkvedge_b200.so")
+TOOLS_LIB_PATH = os.path.join(HERE, "libkvedge_b200_tools.so")
 
 STATIC_SCRATCH_BYTES = 8 << 20  # KV_STATIC_SCRATCH_BYTES of include/kvedge_b200.h
 KV_OK, KV_EINVAL, KV_ENODEVICE, KV_ECUDA, KV_ENOMEM, KV_ECORRUPT, KV_ETEMPLATE = 0, -1, -2, -3, -4, -5, -6
@@ -30,6 +31,7 @@ SIGNATURES = {
                                     C.c_void_p, C.c_size_t, C.c_void_p]),
     "kv_b64enc_batch_dev_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
                                              C.c_void_p, C.c_void_p]),
+    "kv_b64_batch_status_dev": (C.c_int, [C.c_void_p, C.c_void_p]),
     "kv_b64dec_batch_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                                       C.c_void_p]),
@@ -57,6 +59,7 @@ SIGNATURES = {
                                C.POINTER(C.c_size_t)]),
     "kv_free": (None, [C.c_void_p]),
     "kv_set_device": (C.c_int, [C.c_int]),
+    "kv_host_pipeline_config": (C.c_int, [C.c_int64, C.c_int]),
     "kv_shutdown": (None, []),
     "kv_pinned_alloc": (C.c_void_p, [C.c_size_t]),
     "kv_pinned_free": (None, [C.c_void_p]),
@@ -79,17 +82,29 @@ class KvError(RuntimeError):
 
 
 _lib = None
+_path = LIB_PATH
+
+
+def use_tools_build() -> None:
+    """tools/ only: load libkvedge_b200_tools.so (sweep shapes and KVEDGE_* knobs compiled in)
+    instead of the product library.  Must be called before the first lib()."""
+    global _path
+    if _lib is not None:
+        raise RuntimeError("the library is already loaded")
+    from . import build
+    build.build_native(tools=True)
+    _path = TOOLS_LIB_PATH
 
 
 def lib() -> C.CDLL:
     """The loaded library; raises if it has not been built (no silent fallback)."""
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
+        if not os.path.exists(_path):
             raise ImportError(
-                f"{LIB_PATH} is missing: run `python -m kvedge_b200.build` "
+                f"{_path} is missing: run `python -m kvedge_b200.build` "
                 "(or __graft_entry__.build()); there is no CPU fallback")
-        L = C.CDLL(LIB_PATH)
+        L = C.CDLL(_path)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(L, name)
             fn.restype = res

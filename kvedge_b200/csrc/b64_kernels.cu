@@ -22,6 +22,9 @@
 #include "b64_kernels.cuh"
 
 #include <cstdlib>
+#include <map>
+#include <mutex>
+#include <utility>
 
 namespace kvedge {
 
@@ -343,10 +346,14 @@ template <int NLUT>
 __device__ __forceinline__ uint4 encode_groups(uint32_t g0, uint32_t g1, uint32_t g2, uint32_t g3,
                                                const uint16_t *lut) {
     uint4 r;
+#ifdef KVEDGE_TOOLS
     if (NLUT < 0) {  // diagnostic skeleton: memory traffic only, wrong bytes
         r.x = g0; r.y = g1; r.z = g2; r.w = g0 ^ g3;
         return r;
     }
+#else
+    static_assert(NLUT >= 0, "the traffic-only skeleton exists in the tools build only");
+#endif
     r.x = NLUT >= 4 ? encode_group_lut(g0, lut) : encode_group(g0);
     r.y = NLUT >= 1 ? encode_group_lut(g1, lut) : encode_group(g1);
     r.z = NLUT >= 3 ? encode_group_lut(g2, lut) : encode_group(g2);
@@ -357,10 +364,12 @@ __device__ __forceinline__ uint4 encode_groups(uint32_t g0, uint32_t g1, uint32_
 template <int NLUT>
 __device__ __forceinline__ uint4 encode12_mixed(uint32_t a0, uint32_t a1, uint32_t a2, const uint16_t *lut) {
     uint4 r;
+#ifdef KVEDGE_TOOLS
     if (NLUT < 0) {  // diagnostic skeleton (tools/sweep_enc.py): memory traffic only, wrong bytes
         r.x = a0; r.y = a1; r.z = a2; r.w = a0 ^ a2;
         return r;
     }
+#endif
     const uint32_t g0 = __byte_perm(a0, 0u, 0x0124), g1 = __byte_perm(a0, a1, 0x3455);
     const uint32_t g2 = __byte_perm(a1, a2, 0x2344), g3 = __byte_perm(a2, 0u, 0x1233);
     return encode_groups<NLUT>(g0, g1, g2, g3, lut);
@@ -1656,7 +1665,36 @@ int64_t plan_tiles_host(const int64_t *in_off, const int64_t *out_off, int64_t n
 }
 
 // ----------------------------------------------------------------------------- launchers
-static int g_occ_dec = 0;
+// Per (device, kernel): the dynamic-shared-memory opt-in (a per-device function attribute) done
+// and the resident blocks per SM known.  The *_dev entry points may be called from any thread,
+// and a process may hold unlike GPUs, hence the lock and the device in the key.
+namespace {
+std::mutex g_launch_mu;
+std::map<std::pair<int, const void *>, int> g_kernel_occ;
+}  // namespace
+
+static cudaError_t kernel_ready(const void *fn, int threads, size_t dyn, int *occ_out) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lk(g_launch_mu);
+    auto it = g_kernel_occ.find({dev, fn});
+    if (it == g_kernel_occ.end()) {
+        e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+        if (e != cudaSuccess) return e;
+        int occ = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, threads, dyn);
+        if (e != cudaSuccess) return e;
+        it = g_kernel_occ.emplace(std::make_pair(dev, fn), occ > 0 ? occ : 1).first;
+    }
+    *occ_out = it->second;
+    return cudaSuccess;
+}
+
+void reset_launch_caches() {
+    std::lock_guard<std::mutex> lk(g_launch_mu);
+    g_kernel_occ.clear();
+}
 
 static cudaError_t plan(const int64_t *d_in_off, const int64_t *d_out_off, int64_t n_units,
                         int tile_in, int small_max, int mode, const ScratchLayout &L, void *d_scratch,
@@ -1679,16 +1717,63 @@ static cudaError_t plan(const int64_t *d_in_off, const int64_t *d_out_off, int64
                                small_max, (const int *)block_sums, header, desc, (int)L.max_tiles, d_out_len, d_status);
 }
 
-// Which encode kernel a batch gets: the KVEDGE_ENC_VARIANT knob (tools/), and for the default
-// the grouped kernel (200) unless the batch is tiny.  The plan and the run must agree on it,
-// because only the grouped kernels understand group tiles.
+// The encode kernels' shapes.  Entry 0 of each table is the product; the rest are sweep shapes
+// of the tools build (tools/sweep_enc.py), absent from the product library.
+using EncKernel = void (*)(const uint8_t *, char *, const TileDesc *, int *, const int64_t *, int64_t);
+struct EncGroupVariant {
+    EncKernel fn; int groups, stages, consumers, ring;
+    int threads() const { return 32 * groups * (1 + consumers); }
+    size_t dyn() const { return (size_t)groups * (ring ? (size_t)ring : (size_t)stages * stream::kStageStride); }
+};
+static const EncGroupVariant kEncGroup[] = {
+    {stream::b64enc_groups<5, 3, 4, 2, 1, 0>, 5, 3, 4, 0},   // product
+#ifdef KVEDGE_TOOLS
+    {stream::b64enc_groups<6, 3, 4, 2, 1, 0>, 6, 3, 4, 0},
+    {stream::b64enc_groups<6, 8, 4, 2, 1, 36480>, 6, 8, 4, 36480},
+    {stream::b64enc_groups<5, 3, 4, 3, 1, 0>, 5, 3, 4, 0},
+    {stream::b64enc_groups<4, 3, 4, 2, 1, 0>, 4, 3, 4, 0},
+    {stream::b64enc_groups<4, 4, 4, 2, 1, 0>, 4, 4, 4, 0},
+    {stream::b64enc_groups<4, 3, 5, 2, 1, 0>, 4, 3, 5, 0},
+    {stream::b64enc_groups<5, 4, 4, 2, 1, 0>, 5, 4, 4, 0},
+    {stream::b64enc_groups<5, 3, 3, 2, 1, 0>, 5, 3, 3, 0},
+#endif
+};
+struct EncStreamVariant {
+    EncKernel fn; int stages, consumers, ring;
+    int threads() const { return 32 * (1 + consumers); }
+    size_t dyn() const { return ring ? (size_t)ring : (size_t)stages * stream::kStageStride; }
+};
+static const EncStreamVariant kEncStream[] = {
+    {stream::b64enc_stream<3, 8, 0, 4>, 3, 8, 0},            // product, tiny batches: all-arithmetic, no table to fill
+#ifdef KVEDGE_TOOLS
+    {stream::b64enc_stream<4, 8, 2, 3>, 4, 8, 0},
+    {stream::b64enc_stream<3, 8, 1, 4>, 3, 8, 0},  {stream::b64enc_stream<3, 8, 3, 4>, 3, 8, 0},
+    {stream::b64enc_stream<3, 8, 2, 4>, 3, 8, 0},  {stream::b64enc_stream<3, 12, 2, 3>, 3, 12, 0},
+    {stream::b64enc_stream<2, 8, 2, 5>, 2, 8, 0},  {stream::b64enc_stream<4, 12, 2, 3>, 4, 12, 0},
+    {stream::b64enc_stream<3, 16, 2, 2>, 3, 16, 0}, {stream::b64enc_stream<6, 16, 2, 2>, 6, 16, 0},
+    {stream::b64enc_stream<8, 8, 2, 4, 36352>, 8, 8, 36352}, {stream::b64enc_stream<6, 8, 2, 4, 36352>, 6, 8, 36352},
+    {stream::b64enc_stream<12, 8, 2, 4, 36352>, 12, 8, 36352}, {stream::b64enc_stream<8, 8, 2, 3, 57344>, 8, 8, 57344},
+    {stream::b64enc_stream<3, 8, -1, 4>, 3, 8, 0},           // 14: traffic-only skeleton (wrong bytes; tools build only)
+    {stream::b64enc_stream<3, 8, 2, 4, 0, true>, 3, 8, 0}, {stream::b64enc_stream<3, 8, 4, 4>, 3, 8, 0},
+    {stream::b64enc_stream<3, 8, 2, 4>, 3, 8, 0},            // 17: the round-1 one-pipeline kernel
+#endif
+};
+
+// Which encode kernel a batch gets: the grouped kernel (200) unless the batch is tiny (0).  The
+// plan and the run must agree on it, because only the grouped kernels understand group tiles.
+// The product library knows these two and nothing else; the KVEDGE_ENC_VARIANT knob and the
+// other shapes exist only in the tools build (-DKVEDGE_TOOLS, libkvedge_b200_tools.so), so the
+// bytes a caller gets can never depend on its environment.
 static int enc_variant_for(const ScratchLayout &L) {
-    static int latched = -1;
-    if (latched < 0) {
+    int latched = 0;
+#ifdef KVEDGE_TOOLS
+    static const int env_variant = [] {
         const char *v = getenv("KVEDGE_ENC_VARIANT");
-        latched = v ? atoi(v) : 0;
-        if (latched < 0) latched = 0;
-    }
+        const int x = v ? atoi(v) : 0;
+        return x < 0 ? 0 : x;
+    }();
+    latched = env_variant;
+#endif
     return latched == 0 && L.max_tiles > 32 ? 200 : latched;
 }
 int enc_small_max(const ScratchLayout &L) { return enc_variant_for(L) >= 200 ? kEncTileIn / 4 : 0; }
@@ -1708,98 +1793,43 @@ cudaError_t launch_b64enc_run(const uint8_t *d_in, const int64_t *d_in_off, int6
     if (n_units <= 0) return cudaSuccess;
     ScratchLayout L = scratch_layout(n_units, total_in_bytes, kEncTileIn);
     if (scratch_bytes < L.total) return cudaErrorInvalidValue;
-    using EncKernel = void (*)(const uint8_t *, char *, const TileDesc *, int *, const int64_t *, int64_t);
-    // The product kernel is the grouped one (200); a tiny batch (a single render) takes the
-    // one-pipeline, all-arithmetic build below, which has no table to fill.  KVEDGE_ENC_VARIANT=1..
-    // selects the one-pipeline-per-block kernels, 201.. other group shapes.
-    int variant = enc_variant_for(L);
-    cudaError_t e;
+    const int variant = enc_variant_for(L);
+    char *base = static_cast<char *>(d_scratch);
+    const TileDesc *desc = reinterpret_cast<const TileDesc *>(base + L.desc_off);
+    int *header = reinterpret_cast<int *>(base);
     if (variant >= 200) {  // grouped pipelines: several producer/consumer groups per block around one table
-        struct GroupVariant { EncKernel fn; int groups, stages, consumers, ring, lut; };
-        static const GroupVariant kGroup[] = {
-            {stream::b64enc_groups<5, 3, 4, 2, 1, 0>, 5, 3, 4, 0, 2},
-            {stream::b64enc_groups<6, 3, 4, 2, 1, 0>, 6, 3, 4, 0, 2},
-            {stream::b64enc_groups<6, 8, 4, 2, 1, 36480>, 6, 8, 4, 36480, 2},
-            {stream::b64enc_groups<5, 3, 4, 3, 1, 0>, 5, 3, 4, 0, 3},
-            {stream::b64enc_groups<4, 3, 4, 2, 1, 0>, 4, 3, 4, 0, 2},
-            {stream::b64enc_groups<4, 4, 4, 2, 1, 0>, 4, 4, 4, 0, 2},
-            {stream::b64enc_groups<4, 3, 5, 2, 1, 0>, 4, 3, 5, 0, 2},
-            {stream::b64enc_groups<5, 4, 4, 2, 1, 0>, 5, 4, 4, 0, 2},
-            {stream::b64enc_groups<5, 3, 3, 2, 1, 0>, 5, 3, 3, 0, 2}};
-        static int occ_g[16];
-        static bool attr_g[64][16];
-        const int ng = (int)(sizeof kGroup / sizeof *kGroup);
-        const int vi = variant - 200 < ng ? variant - 200 : 0;
-        const GroupVariant &gv = kGroup[vi];
-        const int threads = 32 * gv.groups * (1 + gv.consumers);
-        const size_t dyn = (size_t)gv.groups * (gv.ring ? (size_t)gv.ring : (size_t)gv.stages * stream::kStageStride);
-        int dev = 0;
-        e = cudaGetDevice(&dev);
+        const int ng = (int)(sizeof kEncGroup / sizeof *kEncGroup);
+        const EncGroupVariant &gv = kEncGroup[variant - 200 < ng ? variant - 200 : 0];
+        int occ = 1;
+        cudaError_t e = kernel_ready(reinterpret_cast<const void *>(gv.fn), gv.threads(), gv.dyn(), &occ);
         if (e != cudaSuccess) return e;
-        if (dev >= 0 && dev < 64 && !attr_g[dev][vi]) {
-            e = cudaFuncSetAttribute(gv.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-            if (e != cudaSuccess) return e;
-            attr_g[dev][vi] = true;
-        }
-        if (occ_g[vi] == 0) {
-            int occ = 0;
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gv.fn, threads, dyn);
-            if (e != cudaSuccess) return e;
-            occ_g[vi] = occ > 0 ? occ : 1;
-        }
-        int64_t grid = (int64_t)sm_count * occ_g[vi];
+        int64_t grid = (int64_t)sm_count * occ;
         if (grid > (L.max_tiles + gv.groups - 1) / gv.groups) grid = (L.max_tiles + gv.groups - 1) / gv.groups;
         if (grid < 1) grid = 1;
-        char *base = static_cast<char *>(d_scratch);
-        return launch_after_kernel(gv.fn, dim3((unsigned)grid), dim3(threads), dyn, stream, d_in, d_out,
-                                   reinterpret_cast<const TileDesc *>(base + L.desc_off), reinterpret_cast<int *>(base),
-                                   d_in_off, n_units);
+        return launch_after_kernel(gv.fn, dim3((unsigned)grid), dim3(gv.threads()), gv.dyn(), stream, d_in, d_out, desc,
+                                   header, d_in_off, n_units);
     }
-    {   // one pipeline per block: tiny batches, and KVEDGE_ENC_VARIANT=1..17 for tools/sweep_enc.py
-        struct StreamVariant { EncKernel fn; int stages, consumers, ring; };
-        static const StreamVariant kStream[] = {
-            {stream::b64enc_stream<3, 8, 2, 4>, 3, 8},  {stream::b64enc_stream<4, 8, 2, 3>, 4, 8},
-            {stream::b64enc_stream<3, 8, 1, 4>, 3, 8},  {stream::b64enc_stream<3, 8, 3, 4>, 3, 8},
-            {stream::b64enc_stream<3, 8, 0, 4>, 3, 8},  {stream::b64enc_stream<3, 12, 2, 3>, 3, 12},
-            {stream::b64enc_stream<2, 8, 2, 5>, 2, 8},  {stream::b64enc_stream<4, 12, 2, 3>, 4, 12},
-            {stream::b64enc_stream<3, 16, 2, 2>, 3, 16}, {stream::b64enc_stream<6, 16, 2, 2>, 6, 16},
-            {stream::b64enc_stream<8, 8, 2, 4, 36352>, 8, 8, 36352}, {stream::b64enc_stream<6, 8, 2, 4, 36352>, 6, 8, 36352},
-            {stream::b64enc_stream<12, 8, 2, 4, 36352>, 12, 8, 36352}, {stream::b64enc_stream<8, 8, 2, 3, 57344>, 8, 8, 57344},
-            {stream::b64enc_stream<3, 8, -1, 4>, 3, 8, 0}, {stream::b64enc_stream<3, 8, 2, 4, 0, true>, 3, 8, 0}, {stream::b64enc_stream<3, 8, 4, 4>, 3, 8, 0},
-            {stream::b64enc_stream<3, 8, 2, 4>, 3, 8}};  // 17: the round-1 one-pipeline kernel (was variant 0)
-        static int occ_v[24];
-        const int nv = (int)(sizeof kStream / sizeof *kStream);
-        // tiny batches (a single render): the all-arithmetic build, which has no table to fill
-        const bool tiny = variant == 0;  // only tiny batches still arrive here with variant 0
-        const StreamVariant &sv = kStream[tiny ? 4 : (variant < nv ? variant : 0)];
-        const int threads = 32 * (1 + sv.consumers);
-        const size_t dyn = sv.ring ? (size_t)sv.ring : (size_t)sv.stages * stream::kStageStride;
-        static bool attr_set[64][24];  // per device and variant: the opt-in is a per-device attribute
-        const int vi = (int)(&sv - kStream);
-        int dev = 0;
-        e = cudaGetDevice(&dev);
-        if (e != cudaSuccess) return e;
-        if (dev >= 0 && dev < 64 && !attr_set[dev][vi]) {
-            e = cudaFuncSetAttribute(sv.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-            if (e != cudaSuccess) return e;
-            attr_set[dev][vi] = true;
-        }
-        if (occ_v[vi] == 0) {
-            int occ = 0;
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sv.fn, threads, dyn);
-            if (e != cudaSuccess) return e;
-            occ_v[vi] = occ > 0 ? occ : 1;
-        }
-        int64_t grid = (int64_t)sm_count * occ_v[vi];
-        if (grid > L.max_tiles) grid = L.max_tiles;
-        if (grid < 1) grid = 1;
-        char *base = static_cast<char *>(d_scratch);
-        sv.fn<<<(unsigned)grid, threads, dyn, stream>>>(
-            d_in, d_out, reinterpret_cast<const TileDesc *>(base + L.desc_off),
-            reinterpret_cast<int *>(base), d_in_off, n_units);
-        return cudaGetLastError();
-    }
-    return cudaErrorInvalidValue;   // not reached: every variant was handled above
+    // one pipeline per block: tiny batches (a single render) take the all-arithmetic build, which
+    // has no table to fill
+    const int nv = (int)(sizeof kEncStream / sizeof *kEncStream);
+    const EncStreamVariant &sv = kEncStream[variant < nv ? variant : 0];
+    int occ = 1;
+    cudaError_t e = kernel_ready(reinterpret_cast<const void *>(sv.fn), sv.threads(), sv.dyn(), &occ);
+    if (e != cudaSuccess) return e;
+    int64_t grid = (int64_t)sm_count * occ;
+    if (grid > L.max_tiles) grid = L.max_tiles;
+    if (grid < 1) grid = 1;
+    sv.fn<<<(unsigned)grid, sv.threads(), sv.dyn(), stream>>>(d_in, d_out, desc, header, d_in_off, n_units);
+    return cudaGetLastError();
+}
+
+// Opt-ins and occupancy queries of every kernel the product may launch, done now for the current
+// device (kv_b64enc_batch_dev_static's set-up: nothing of the kind is left for a later call).
+cudaError_t warm_b64enc_kernels() {
+    int occ = 0;
+    cudaError_t e = kernel_ready(reinterpret_cast<const void *>(kEncGroup[0].fn), kEncGroup[0].threads(), kEncGroup[0].dyn(), &occ);
+    if (e != cudaSuccess) return e;
+    return kernel_ready(reinterpret_cast<const void *>(kEncStream[0].fn), kEncStream[0].threads(), kEncStream[0].dyn(), &occ);
 }
 
 cudaError_t launch_b64enc(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_units,
@@ -1813,29 +1843,40 @@ cudaError_t launch_b64enc(const uint8_t *d_in, const int64_t *d_in_off, int64_t 
                              scratch_bytes, stream, sm_count);
 }
 
-// The streamed decode kernel's shapes.  Entry 0 is the product; the others are kept for
-// tools/sweep_dec.py (KVEDGE_DEC_VARIANT=n).
+// The streamed decode kernel's shapes.  Entry 0 is the product; the others exist only in the
+// tools build (tools/sweep_dec.py, KVEDGE_DEC_VARIANT=n).
 using DecKernel = void (*)(const char *, uint8_t *, const TileDesc *, int *, const int64_t *, int64_t,
                            int64_t *, int64_t *);
-struct DecVariant { DecKernel fn; int groups, stages, consumers, tile, ring; };
+struct DecVariant {
+    DecKernel fn; int groups, stages, consumers, tile, ring;
+    int threads() const { return 32 * groups * (1 + consumers); }
+    size_t dyn() const {
+        return (size_t)stream::kDecLutBytes + (size_t)groups * (ring ? (size_t)ring : (size_t)stages * stream::dec_stage_stride(tile));
+    }
+};
 static const DecVariant kDec[] = {
     {stream::b64dec_stream<5, 8, 5, 1, 16384, 40448>, 5, 8, 5, 16384, 40448},  // product
+#ifdef KVEDGE_TOOLS
     {stream::b64dec_stream<1, 3, 8, 4, 16384>, 1, 3, 8, 16384, 0},             // one pipeline per block, 3 blocks/SM
     {stream::b64dec_stream<6, 2, 4, 1, 16384>, 6, 2, 4, 16384, 0},             // grouped, fixed slots
     {stream::b64dec_stream<5, 4, 5, 1, 16384, 40960>, 5, 4, 5, 16384, 40960},
     {stream::b64dec_stream<6, 4, 4, 1, 16384, 34256>, 6, 4, 4, 16384, 34256},
     {stream::b64dec_stream<5, 8, 4, 1, 16384, 40448>, 5, 8, 4, 16384, 40448},
-    {stream::b64dec_stream<4, 8, 6, 1, 16384, 50688>, 4, 8, 6, 16384, 50688}};
+    {stream::b64dec_stream<4, 8, 6, 1, 16384, 50688>, 4, 8, 6, 16384, 50688},
+#endif
+};
 
 static int dec_variant() {
-    static int v = -1;
-    if (v < 0) {
+#ifdef KVEDGE_TOOLS
+    static const int v = [] {
         const char *e = getenv("KVEDGE_DEC_VARIANT");
-        int x = e ? atoi(e) : 0;
-        if (x < 0 || x >= (int)(sizeof kDec / sizeof *kDec)) x = 0;
-        v = x;
-    }
+        const int x = e ? atoi(e) : 0;
+        return x < 0 || x >= (int)(sizeof kDec / sizeof *kDec) ? 0 : x;
+    }();
     return v;
+#else
+    return 0;
+#endif
 }
 
 int dec_tile_in() { return kDec[dec_variant()].tile; }
@@ -1864,37 +1905,18 @@ cudaError_t launch_b64dec_run(const char *d_in, const int64_t *d_in_off, int64_t
     if (n_units <= 0) return cudaSuccess;
     ScratchLayout L = scratch_layout(n_units, total_in_bytes, dec_tile_in());
     if (scratch_bytes < L.total) return cudaErrorInvalidValue;
-    cudaError_t e;
-    const int variant = dec_variant();
     char *base = static_cast<char *>(d_scratch);
-    {
-        const DecVariant &dv = kDec[variant];
-        const int threads = 32 * dv.groups * (1 + dv.consumers);
-        const size_t dyn = (size_t)stream::kDecLutBytes + (size_t)dv.groups * (dv.ring ? (size_t)dv.ring : (size_t)dv.stages * stream::dec_stage_stride(dv.tile));
-        // the dynamic-shared-memory opt-in is a per-device function attribute
-        static bool dec_attr_set[64];
-        int dev = 0;
-        e = cudaGetDevice(&dev);
-        if (e != cudaSuccess) return e;
-        if (dev >= 0 && dev < 64 && !dec_attr_set[dev]) {
-            e = cudaFuncSetAttribute(dv.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-            if (e != cudaSuccess) return e;
-            dec_attr_set[dev] = true;
-        }
-        if (g_occ_dec == 0) {
-            int occ = 0;
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dv.fn, threads, dyn);
-            if (e != cudaSuccess) return e;
-            g_occ_dec = occ > 0 ? occ : 1;
-        }
-        int64_t grid = (int64_t)sm_count * g_occ_dec;
-        if (grid > (L.max_tiles + dv.groups - 1) / dv.groups) grid = (L.max_tiles + dv.groups - 1) / dv.groups;
-        if (grid < 1) grid = 1;
-        e = launch_after_kernel(dv.fn, dim3((unsigned)grid), dim3(threads), dyn, stream, d_in, d_out,
-                                reinterpret_cast<const TileDesc *>(base + L.desc_off), reinterpret_cast<int *>(base),
-                                d_in_off, n_units, d_out_len, d_status);
-        if (e != cudaSuccess) return e;
-    }
+    const DecVariant &dv = kDec[dec_variant()];
+    int occ = 1;
+    cudaError_t e = kernel_ready(reinterpret_cast<const void *>(dv.fn), dv.threads(), dv.dyn(), &occ);
+    if (e != cudaSuccess) return e;
+    int64_t grid = (int64_t)sm_count * occ;
+    if (grid > (L.max_tiles + dv.groups - 1) / dv.groups) grid = (L.max_tiles + dv.groups - 1) / dv.groups;
+    if (grid < 1) grid = 1;
+    e = launch_after_kernel(dv.fn, dim3((unsigned)grid), dim3(dv.threads()), dv.dyn(), stream, d_in, d_out,
+                            reinterpret_cast<const TileDesc *>(base + L.desc_off), reinterpret_cast<int *>(base),
+                            d_in_off, n_units, d_out_len, d_status);
+    if (e != cudaSuccess) return e;
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     int64_t sg = (n_units + 127) / 128;

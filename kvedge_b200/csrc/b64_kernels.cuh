@@ -76,4 +76,10 @@ int64_t plan_tiles_host(const int64_t *in_off, const int64_t *out_off, int64_t n
                         const int64_t *d_out_off, int64_t *out_len, int64_t *status);
 int enc_small_max(const ScratchLayout &L);
 
+// Shared-memory opt-in and occupancy of every encode kernel the product launches, for the
+// current device, now (otherwise the first launch of each kernel does it).
+cudaError_t warm_b64enc_kernels();
+// Forget the per-device launch set-up (kv_shutdown).
+void reset_launch_caches();
+
 }  // namespace kvedge

@@ -58,6 +58,8 @@ int sm_count_of_current_device(int *out) {
     int dev = 0;
     KV_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) return fail(KV_EINVAL, "device index %d out of range", dev);
+    static std::mutex mu;   // the *_dev entries may come from any thread
+    std::lock_guard<std::mutex> lk(mu);
     if (g_sm_count[dev] == 0) {
         int n = 0;
         KV_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
@@ -71,24 +73,20 @@ int sm_count_of_current_device(int *out) {
 constexpr int kSlots = 8;       // slots that exist; n_slots() of them are used
 constexpr int64_t kChunkBytesDefault = 16ll << 20;  // input bytes per pipeline chunk
 
-int n_slots() {
-    static int v = 0;
-    if (v == 0) {  // KVEDGE_SLOTS: tuning knob for tools/
-        const char *e = getenv("KVEDGE_SLOTS");
-        v = e && atoi(e) > 0 ? atoi(e) : 4;
-        if (v > kSlots) v = kSlots;
-    }
-    return v;
+// Chunk size and slots in use: kv_host_pipeline_config() (an explicit call, under g_mu).  The
+// diagnostic knobs KVEDGE_TRACE and KVEDGE_E2E_DIAG exist in the tools build only
+// (-DKVEDGE_TOOLS, libkvedge_b200_tools.so): the product library reads no environment variable,
+// so what a caller gets never depends on its environment.
+int g_n_slots = 4;
+int64_t g_chunk_bytes = kChunkBytesDefault;
+int n_slots() { return g_n_slots; }
+int64_t chunk_bytes() { return g_chunk_bytes; }
+#ifdef KVEDGE_TOOLS
+int env_int(const char *name, int dflt) {
+    const char *e = getenv(name);
+    return e && atoi(e) > 0 ? atoi(e) : dflt;
 }
-
-int64_t chunk_bytes() {
-    static int64_t v = 0;
-    if (v == 0) {  // KVEDGE_CHUNK_MB: tuning knob for tools/
-        const char *e = getenv("KVEDGE_CHUNK_MB");
-        v = e && atoi(e) > 0 ? (int64_t)atoi(e) << 20 : kChunkBytesDefault;
-    }
-    return v;
-}
+#endif
 
 // A slot owns the device buffers of one chunk in flight.  Three streams carry the batch --
 // uploads, kernels, downloads -- and events chain a chunk through them, so the host submits the
@@ -167,11 +165,14 @@ int ctx_init() {
 // KVEDGE_TRACE=1: per-chunk device timeline of a host batch on stderr (tools/ only).
 struct ChunkTrace { cudaEvent_t e[4]; double host[5]; };  // before H2D, after H2D, after kernel, after D2H; host clock at each mark
 std::vector<ChunkTrace> g_trace;
+#ifdef KVEDGE_TOOLS
 bool trace_on() {
-    static int v = -1;
-    if (v < 0) { const char *e = getenv("KVEDGE_TRACE"); v = e && atoi(e) > 0 ? 1 : 0; }
-    return v == 1;
+    static const bool v = env_int("KVEDGE_TRACE", 0) > 0;
+    return v;
 }
+#else
+constexpr bool trace_on() { return false; }
+#endif
 void trace_mark(int which, cudaStream_t st) {
     if (!trace_on()) return;
     if (which == 0) {
@@ -274,8 +275,11 @@ int run_chunk(Slot &s, int mode, const char *in, const int64_t *in_off, char *ou
     int64_t *d_len = reinterpret_cast<int64_t *>(s.d_ctl + off_len);
     int64_t *d_status = reinterpret_cast<int64_t *>(s.d_ctl + off_status);
     cudaError_t e = cudaSuccess;
-    static int diag = -1;  // KVEDGE_E2E_DIAG (tools/ only): 1 = no kernel, 2 = also no upload->download ordering
-    if (diag < 0) { const char *d = getenv("KVEDGE_E2E_DIAG"); diag = d ? atoi(d) : 0; }
+#ifdef KVEDGE_TOOLS
+    static const int diag = env_int("KVEDGE_E2E_DIAG", 0);  // 1 = no kernel, 2 = also no upload->download ordering
+#else
+    constexpr int diag = 0;
+#endif
     if (n_tiles > 0 && diag == 0) {
         if (mode == 0)
             e = kvedge::launch_b64enc_run(reinterpret_cast<const uint8_t *>(d_input), d_in_off, n,
@@ -448,6 +452,18 @@ int kv_b64enc_run_dev(const uint8_t *d_in, const int64_t *d_in_off, int64_t n_un
     return KV_OK;
 }
 
+int kv_b64_batch_status_dev(const void *d_scratch, void *stream) {
+    if (!d_scratch) return fail(KV_EINVAL, "null scratch");
+    int header[4] = {0, 0, 0, 0};
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    KV_CUDA(cudaMemcpyAsync(header, d_scratch, sizeof header, cudaMemcpyDeviceToHost, st));
+    KV_CUDA(cudaStreamSynchronize(st));
+    if (header[3] != 0)
+        return fail(KV_EINVAL, "the batch was truncated: total_in_bytes understated d_in_off[n_units], the tile table "
+                               "held %d tiles and units beyond them were not processed", header[0]);
+    return KV_OK;
+}
+
 int kv_b64dec_batch_dev(const char *d_in, const int64_t *d_in_off, int64_t n_units,
                         int64_t total_in_bytes, uint8_t *d_out, const int64_t *d_out_off,
                         int64_t *d_out_len, int64_t *d_status, void *d_scratch,
@@ -505,6 +521,15 @@ int kv_b64dec(const char *in, size_t n, uint8_t *out, size_t *out_n, size_t *err
     return KV_OK;
 }
 
+int kv_host_pipeline_config(int64_t chunk_bytes_, int slots) {
+    if (chunk_bytes_ < 0 || slots < 0 || slots > kSlots)
+        return fail(KV_EINVAL, "chunk_bytes must be >= 0 and slots within 0..%d", kSlots);
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (chunk_bytes_ > 0) g_chunk_bytes = std::max<int64_t>(chunk_bytes_, 64 << 10);
+    if (slots > 0) g_n_slots = std::max(slots, 2);
+    return KV_OK;
+}
+
 int kv_set_device(int device) {
     std::lock_guard<std::mutex> lk(g_mu);
     if (g_ctx.ready && device != g_ctx.device)
@@ -558,6 +583,7 @@ void kv_shutdown(void) {
     if (g_ctx.s_down) cudaStreamDestroy(g_ctx.s_down);
     g_ctx.s_up = g_ctx.s_run = g_ctx.s_down = nullptr;
     g_ctx.ready = false;
+    kvedge::reset_launch_caches();
 }
 
 }  // extern "C"

@@ -715,7 +715,7 @@ static const char *kInstallOrder[] = {
     "PersistentVolumeClaim", "CustomResourceDefinition", "ClusterRole", "ClusterRoleList",
     "ClusterRoleBinding", "ClusterRoleBindingList", "Role", "RoleList", "RoleBinding", "RoleBindingList",
     "Service", "DaemonSet", "Pod", "ReplicationController", "ReplicaSet", "Deployment",
-    "HorizontalPodAutoscaler", "StatefulSet", "Job", "CronJob", "Ingress", "APIService"};
+    "HorizontalPodAutoscaler", "StatefulSet", "Job", "CronJob", "IngressClass", "Ingress", "APIService"};
 
 static int install_rank(const std::string &kind) {
     for (size_t i = 0; i < sizeof kInstallOrder / sizeof *kInstallOrder; ++i)
@@ -723,24 +723,31 @@ static int install_rank(const std::string &kind) {
     return -1;
 }
 
-// Split on lines that are "---" followed only by white space (Go: (?m)^---\s*$).
+// releaseutil.SplitManifests: strings.Split on the regexp `(?:^|\s*\n)---\s*` -- "---" at the very
+// start of the text or right after a newline; the white space in front of that newline and
+// behind the dashes belongs to the separator, and whatever follows the dashes on their line
+// starts the next document.  (Go's \s is [\t\n\f\r ].)
+static bool re_space(char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\f' || c == '\r'; }
 static std::vector<std::string> split_docs(const std::string &s) {
     std::vector<std::string> docs;
     size_t start = 0, i = 0;
-    while (i <= s.size()) {
-        size_t j = s.find('\n', i);
-        if (j == std::string::npos) j = s.size();
-        bool sep = s.compare(i, 3, "---") == 0;
-        if (sep)
-            for (size_t k = i + 3; k < j; ++k)
-                if (!is_ws(s[k])) sep = false;
-        if (sep) {
-            docs.push_back(s.substr(start, i - start));
-            start = j < s.size() ? j + 1 : j;
+    for (;;) {
+        size_t ms, me;
+        if (i == 0 && s.compare(0, 3, "---") == 0) {
+            ms = 0;
+            me = 3;
+        } else {
+            const size_t p = s.find("\n---", i);
+            if (p == std::string::npos) break;
+            ms = p;
+            while (ms > i && re_space(s[ms - 1])) --ms;
+            me = p + 4;
         }
-        i = j + 1;
+        while (me < s.size() && re_space(s[me])) ++me;
+        docs.push_back(s.substr(start, ms - start));
+        start = i = me;
     }
-    docs.push_back(start <= s.size() ? s.substr(start) : "");
+    docs.push_back(s.substr(start));
     return docs;
 }
 

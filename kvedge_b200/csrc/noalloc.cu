@@ -13,6 +13,15 @@
 // carries it until the process exits, batches whose tile table would not fit are refused,
 // and because every call uses the same array, two calls must not be in flight on one GPU
 // at the same time.
+//
+// "Allocates nothing" is a statement about this library's calls: no cudaMalloc, cudaFree or
+// allocating library routine, ever.  The CUDA driver, however, loads a module's code and
+// global arrays into device memory when the module is first touched, and for this file that
+// moment is the first call on a device (the cudaGetSymbolAddress below): that call needs
+// room for the 8 MiB array and the kernels' code, so it belongs in start-up code, BEFORE the
+// other party claims the rest of the memory and outside any stream capture.  The same first
+// call does the kernels' one-time launch set-up for both the large-batch and the tiny-batch
+// kernel, so later calls do no set-up of any kind.
 #include "../../include/kvedge_b200.h"
 
 #include <cuda_runtime.h>
@@ -56,6 +65,10 @@ int setup_current_device(int *dev_out) {
         int sms = 0;
         e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (e != cudaSuccess) return fail(KV_ECUDA, std::string("cudaDeviceGetAttribute: ") + cudaGetErrorString(e));
+        // every launch-time set-up the encode kernels would otherwise do on first use -- the large-
+        // batch and the tiny-batch kernel alike -- so that no later call has any left to do
+        e = kvedge::warm_b64enc_kernels();
+        if (e != cudaSuccess) return fail(KV_ECUDA, std::string("kernel set-up: ") + cudaGetErrorString(e));
         g_sm_count[dev] = sms;
         g_scratch_addr[dev] = p;
     }

@@ -395,7 +395,11 @@ int kv_helm_template(const char *chart_dir, const char *release_name, const char
 int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *release_names, const char *ns,
                       const kv_overrides *overrides, char **out, int64_t *out_off) {
     if (!chart || n_releases < 0 || !out || !out_off) return fail(KV_EINVAL, "null argument");
-    const bool trace = getenv("KVEDGE_TRACE") && atoi(getenv("KVEDGE_TRACE")) > 0;
+#ifdef KVEDGE_TOOLS
+    const bool trace = getenv("KVEDGE_TRACE") && atoi(getenv("KVEDGE_TRACE")) > 0;   // tools build only
+#else
+    constexpr bool trace = false;
+#endif
     auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     const double t_start = now();
     double t_prev = t_start;

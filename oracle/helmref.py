@@ -421,9 +421,10 @@ INSTALL_ORDER = [
     "ClusterRoleList", "ClusterRoleBinding", "ClusterRoleBindingList", "Role", "RoleList",
     "RoleBinding", "RoleBindingList", "Service", "DaemonSet", "Pod", "ReplicationController",
     "ReplicaSet", "Deployment", "HorizontalPodAutoscaler", "StatefulSet", "Job", "CronJob",
-    "Ingress", "APIService",
+    "IngressClass", "Ingress", "APIService",
 ]
-_SEP = re.compile(rb"(?m)^---\s*$")
+# releaseutil.SplitManifests' separator, verbatim; Go's \s is [\t\n\f\r ] (no \v)
+_SEP = re.compile(rb"(?:^|[\t\n\f\r ]*\n)---[\t\n\f\r ]*")
 _KIND = re.compile(rb"(?m)^kind:[ \t]*([^\s#]+)")
 
 

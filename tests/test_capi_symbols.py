@@ -60,3 +60,13 @@ def test_product_package_never_imports_the_oracle():
                 text = open(os.path.join(dirpath, fn), errors="replace").read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), fn
                 assert "liboracle" not in text and "b64_ref" not in text, fn
+
+
+def test_product_library_reads_no_environment_knob():
+    """The sweep shapes, the traffic-only skeleton kernel and the KVEDGE_* knobs are compiled into
+    libkvedge_b200_tools.so only: what the product library computes cannot depend on the
+    caller's environment."""
+    raw = open(_lib.LIB_PATH, "rb").read()
+    assert b"KVEDGE_" not in raw
+    # exactly the product kernels: one grouped encoder, the tiny-batch encoder, one decoder
+    assert raw.count(b"b64enc_groupsILi") > 0 and b"b64enc_streamILi3ELi8ELin1" not in raw

@@ -394,3 +394,68 @@ def test_pinned_buffers_from_the_library(torch_cuda):
         a = int(out_off[i])
         assert raw[a:a + b64.encoded_len(len(u))] == ob64.encode(u), i
     del h_in, h_out          # finalizers return the memory with kv_pinned_free
+
+
+def test_plan_then_run_equals_batch_equals_oracle(torch_cuda):
+    """kv_b64enc_plan_dev + kv_b64enc_run_dev (the pair bench.py times for `roofline`) against
+    kv_b64enc_batch_dev and the oracle; the run is repeated over the same plan with new bytes,
+    which is what the split exists for."""
+    torch = torch_cuda
+    rng = np.random.default_rng(21)
+    units = _short_and_long_units(rng, 3000)
+    blob, in_off = workload.pack(units)
+    out_off = b64.encode_offsets(in_off, align=16)
+    n = len(units)
+    d_in_off, d_out_off = torch.from_numpy(in_off).cuda(), torch.from_numpy(out_off).cuda()
+    scratch = torch.empty(b64.scratch_bytes(n, len(blob)), dtype=torch.uint8, device="cuda")
+    b64.b64enc_plan_device(d_in_off, d_out_off, scratch, len(blob))
+    for rep in range(3):
+        data = blob if rep == 0 else rng.integers(0, 256, len(blob), dtype=np.uint8)
+        d_in = torch.from_numpy(data).cuda()
+        got = torch.full((int(out_off[-1]),), 0x7E, dtype=torch.uint8, device="cuda")
+        b64.b64enc_run_device(d_in, d_in_off, got, scratch, len(blob))
+        whole = torch.full((int(out_off[-1]),), 0x7E, dtype=torch.uint8, device="cuda")
+        scratch2 = torch.empty_like(scratch)
+        b64.b64enc_device(d_in, d_in_off, whole, d_out_off, scratch2, total_in_bytes=len(blob))
+        torch.cuda.synchronize()
+        assert torch.equal(got, whole), rep
+        ref = ob64.encode_batch(data, in_off, out_off)
+        raw = got.cpu().numpy()
+        for i in range(n):
+            a, b = int(out_off[i]), int(out_off[i]) + b64.encoded_len(int(in_off[i + 1] - in_off[i]))
+            assert np.array_equal(raw[a:b], ref[a:b]), (rep, i)
+            assert (raw[b:int(out_off[i + 1])] == 0x7E).all(), (rep, i)      # nothing outside a unit's range
+    from kvedge_b200 import _lib
+    assert _lib.lib().kv_b64_batch_status_dev(scratch.data_ptr(), None) == _lib.KV_OK
+
+
+def test_understated_total_in_bytes_is_reported_not_silent(torch_cuda):
+    """A caller that passes total_in_bytes < d_in_off[n_units] gets a clamped tile table (memory
+    stays intact, later units are not encoded); kv_b64_batch_status_dev says so."""
+    torch = torch_cuda
+    from kvedge_b200 import _lib
+    L = _lib.lib()
+    units = [bytes([65 + i % 26]) * 40000 for i in range(64)]       # 4 tiles each, 256 in all
+    blob, in_off = workload.pack(units)
+    out_off = b64.encode_offsets(in_off, align=16)
+    d_in = torch.from_numpy(blob).cuda()
+    d_in_off, d_out_off = torch.from_numpy(in_off).cuda(), torch.from_numpy(out_off).cuda()
+    d_out = torch.full((int(out_off[-1]) + 64,), 0x7E, dtype=torch.uint8, device="cuda")
+    lied = len(blob) // 4                                             # table sized for ~116 tiles
+    scratch = torch.full((b64.scratch_bytes(len(units), len(blob)) + 4096,), 0x5A, dtype=torch.uint8, device="cuda")
+    need = b64.scratch_bytes(len(units), lied)
+    _lib.check(L.kv_b64enc_batch_dev(d_in.data_ptr(), d_in_off.data_ptr(), len(units), lied, d_out.data_ptr(),
+                                     d_out_off.data_ptr(), scratch.data_ptr(), need, None))
+    assert L.kv_b64_batch_status_dev(scratch.data_ptr(), None) == _lib.KV_EINVAL
+    assert b"truncated" in L.kv_last_error()
+    assert bool((scratch[need:] == 0x5A).all())                       # nothing written past the table it was given
+    assert bool((d_out[int(out_off[-1]):] == 0x7E).all())
+    raw = d_out.cpu().numpy().tobytes()
+    assert raw[:b64.encoded_len(40000)] == ob64.encode(units[0])      # what was encoded is right
+    # the honest call on the same scratch clears the verdict
+    _lib.check(L.kv_b64enc_batch_dev(d_in.data_ptr(), d_in_off.data_ptr(), len(units), len(blob), d_out.data_ptr(),
+                                     d_out_off.data_ptr(), scratch.data_ptr(), scratch.numel(), None))
+    assert L.kv_b64_batch_status_dev(scratch.data_ptr(), None) == _lib.KV_OK
+    raw = d_out.cpu().numpy().tobytes()
+    for i, u in enumerate(units):
+        assert raw[int(out_off[i]):int(out_off[i]) + b64.encoded_len(len(u))] == ob64.encode(u), i

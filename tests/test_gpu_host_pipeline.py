@@ -1,8 +1,8 @@
 """The host-buffer entry points (kv_b64enc_batch / kv_b64dec_batch) cut a batch into chunks and
 chain them through upload / kernel / download streams.  These cases force many chunks through few
 slots (so every slot is reused several times) and feed host pointers at every alignment the
-upload's head/body split has to deal with.  Run in a subprocess because the chunk size and the
-slot count are latched at first use."""
+upload's head/body split has to deal with.  Run in a subprocess so that the small chunk size set
+through kv_host_pipeline_config does not leak into the other tests."""
 import os
 import subprocess
 import sys
@@ -28,6 +28,7 @@ while sum(sizes) < 24 << 20:
 units = [rng.bytes(s) for s in sizes]
 blob, in_off = workload.pack(units)
 L = _lib.lib()
+_lib.check(L.kv_host_pipeline_config(%(chunk_mb)d << 20, %(slots)d))
 for skew_in, skew_out, align in ((0, 0, 16), (1, 0, 16), (255, 3, 4), (17, 1, 1), (256, 16, 16)):
     out_off = b64.encode_offsets(in_off, align=align)
     hin = np.zeros(len(blob) + 512, dtype=np.uint8)
@@ -56,7 +57,7 @@ print("ok", len(units))
 
 @pytest.mark.parametrize("chunk_mb,slots", [(1, 2), (2, 3)])
 def test_many_chunks_through_few_slots(chunk_mb, slots):
-    env = dict(os.environ, KVEDGE_CHUNK_MB=str(chunk_mb), KVEDGE_SLOTS=str(slots))
-    res = subprocess.run([sys.executable, "-c", SCRIPT % {"root": ROOT}], env=env, capture_output=True, text=True, timeout=600)
+    script = SCRIPT % {"root": ROOT, "chunk_mb": chunk_mb, "slots": slots}
+    res = subprocess.run([sys.executable, "-c", script], capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout + res.stderr
     assert res.stdout.startswith("ok")

@@ -228,3 +228,25 @@ def test_user_lists_replace_chart_lists_and_tables_merge():
     assert m == helmref.helm_template(FIXTURE, "rel6", set_args=sets)
     assert b"9100" not in m and b"2222" in m          # the list was replaced, not patched
     assert b'team: "iot"' in m and b'tier: "edge"' in m and b"zone:" not in m
+
+
+def test_multi_document_template_files_split_like_helm(tmp_path):
+    """releaseutil.SplitManifests splits on `(?:^|\\s*\\n)---\\s*`: white space in front of a
+    separator leaves the document before it, text behind the dashes opens the next one, and a
+    leading `---` is swallowed.  IngressClass sorts in front of Ingress (Helm 3.7 InstallOrder)."""
+    d = tmp_path / "multi"
+    (d / "templates").mkdir(parents=True)
+    (d / "Chart.yaml").write_text("apiVersion: v2\nname: multi\nversion: 0.1.0\n")
+    (d / "values.yaml").write_text("v: hello\n")
+    (d / "templates" / "a.yaml").write_text(
+        "---\nkind: Secret\nk: {{ .Values.v | b64enc }}\n\n---\nkind: ConfigMap\nname: one\n  \n\n--- # next\n"
+        "kind: Ingress\n---\nkind: IngressClass\n---   \n\n---\nkind: Pod\n")
+    r = _plan_and_fill(str(d), "r")
+    got = r.manifest()
+    assert got == helmref.helm_template(str(d), "r")
+    src = b"---\n# Source: multi/templates/a.yaml\n"
+    assert got == (src + b"kind: Secret\nk: aGVsbG8=\n" + src + b"kind: ConfigMap\nname: one\n" +
+                   # "---   \n\n---": the first separator eats the newlines, so the second run of dashes has no
+                   # newline in front of it any more and stays in the document (Go regexp semantics)
+                   src + b"---\nkind: Pod\n" +
+                   src + b"kind: IngressClass\n" + src + b"# next\nkind: Ingress\n")

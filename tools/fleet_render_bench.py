@@ -6,6 +6,8 @@ import ctypes as C
 import json, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+from kvedge_b200 import _lib as _kvlib
+_kvlib.use_tools_build()   # sweep shapes and KVEDGE_* knobs live in libkvedge_b200_tools.so only
 import numpy as np
 from kvedge_b200 import helm, workload, _lib
 from kvedge_b200._lib import KvOverrides

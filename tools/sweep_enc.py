@@ -4,6 +4,8 @@
 import json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+from kvedge_b200 import _lib as _kvlib
+_kvlib.use_tools_build()   # sweep shapes and KVEDGE_* knobs live in libkvedge_b200_tools.so only
 import numpy as np, torch
 import bench
 from kvedge_b200 import b64

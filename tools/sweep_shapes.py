@@ -4,6 +4,8 @@ bench fleet, to see that the kernels are not tuned to one shape only.  One JSON 
 import json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+from kvedge_b200 import _lib as _kvlib
+_kvlib.use_tools_build()   # sweep shapes and KVEDGE_* knobs live in libkvedge_b200_tools.so only
 import numpy as np, torch
 from kvedge_b200 import b64
 from oracle import b64 as ob64
