@@ -468,18 +468,20 @@ Value parse_yaml(const std::string &text, bool json_numbers) {
 // ============================================================================ strvals
 namespace {
 
-Value set_typed(const std::string &val, bool force_string) {
-    if (force_string) return Value::str(val);
-    std::string low = val;
-    for (auto &c : low) c = (char)tolower((unsigned char)c);
-    if (low == "true") return Value::boolean(true);
-    if (low == "false") return Value::boolean(false);
-    if (low == "null") return Value::nil();
+Value set_typed(std::string val, bool force_string) {
+    if (force_string) return Value::str(std::move(val));
+    if (val.size() <= 5) {   // strings.EqualFold(val, "true" / "false" / "null")
+        char low[6] = {0, 0, 0, 0, 0, 0};
+        for (size_t k = 0; k < val.size(); ++k) low[k] = (char)tolower((unsigned char)val[k]);
+        if (!strcmp(low, "true")) return Value::boolean(true);
+        if (!strcmp(low, "false")) return Value::boolean(false);
+        if (!strcmp(low, "null")) return Value::nil();
+    }
     if (val == "0") return Value::integer(0);
-    if (!val.empty() && val[0] != '0') {
+    if (!val.empty() && val[0] != '0' && val.size() <= 20) {
         size_t i = (val[0] == '-' || val[0] == '+') ? 1 : 0;
         bool digits = i < val.size();
-        for (size_t k = i; k < val.size(); ++k)
+        for (size_t k = i; k < val.size() && digits; ++k)
             if (!isdigit((unsigned char)val[k])) digits = false;
         if (digits) {
             errno = 0;
@@ -487,36 +489,49 @@ Value set_typed(const std::string &val, bool force_string) {
             if (errno == 0) return Value::integer(v);
         }
     }
-    return Value::str(val);
+    return Value::str(std::move(val));
 }
 
+// key=value[,key=value...]: runs of ordinary characters are appended whole (a value is often a
+// 400-character SSH key), only backslashes and the three delimiters are looked at one by one.
 std::vector<std::pair<std::string, std::string>> split_set(const std::string &s) {
     std::vector<std::pair<std::string, std::string>> pairs;
+    const char *p = s.data();
     size_t i = 0, n = s.size();
     while (i < n) {
         std::string key;
-        while (i < n && s[i] != '=') {
-            if (s[i] == '\\' && i + 1 < n) { key += s.substr(i, 2); i += 2; continue; }
-            if (s[i] == ',') throw Error("key \"" + key + "\" has no value");
-            key.push_back(s[i++]);
+        for (;;) {
+            size_t j = i;
+            while (j < n && p[j] != '=' && p[j] != '\\' && p[j] != ',') ++j;
+            key.append(p + i, j - i);
+            i = j;
+            if (i >= n || p[i] == '=') break;
+            if (p[i] == '\\' && i + 1 < n) { key.append(p + i, 2); i += 2; continue; }
+            if (p[i] == ',') throw Error("key \"" + key + "\" has no value");
+            key.push_back(p[i++]);   // a lone backslash at the very end
         }
         if (i >= n) throw Error("key \"" + key + "\" has no value");
         ++i;
         std::string val;
-        if (i < n && s[i] == '{') {
+        if (i < n && p[i] == '{') {
             size_t j = s.find('}', i);
             if (j == std::string::npos) throw Error("list must terminate with '}'");
             val = s.substr(i, j + 1 - i);
             i = j + 1;
-            if (i < n && s[i] == ',') ++i;
+            if (i < n && p[i] == ',') ++i;
         } else {
-            while (i < n) {
-                if (s[i] == '\\' && i + 1 < n) { val.push_back(s[i + 1]); i += 2; continue; }
-                if (s[i] == ',') { ++i; break; }
-                val.push_back(s[i++]);
+            for (;;) {
+                size_t j = i;
+                while (j < n && p[j] != '\\' && p[j] != ',') ++j;
+                val.append(p + i, j - i);
+                i = j;
+                if (i >= n) break;
+                if (p[i] == '\\' && i + 1 < n) { val.push_back(p[i + 1]); i += 2; continue; }
+                if (p[i] == ',') { ++i; break; }
+                val.push_back(p[i++]);
             }
         }
-        pairs.push_back({key, val});
+        pairs.emplace_back(std::move(key), std::move(val));
     }
     return pairs;
 }
@@ -543,7 +558,7 @@ std::vector<PathElem> split_key(const std::string &key) {
     return parts;
 }
 
-void assign(Value &root, const std::vector<PathElem> &path, const Value &value) {
+void assign(Value &root, const std::vector<PathElem> &path, Value value) {
     if (root.kind != Value::MapK) root = Value::make_map();
     Value *cur = &root;
     for (size_t k = 0; k < path.size(); ++k) {
@@ -558,7 +573,7 @@ void assign(Value &root, const std::vector<PathElem> &path, const Value &value) 
             if (cur->kind != Value::MapK) throw Error("--set: key \"" + path[k].key + "\" addresses a list, not a map");
             slot = &(*cur->map)[path[k].key];
         }
-        if (last) { *slot = value; return; }
+        if (last) { *slot = std::move(value); return; }
         if (slot->kind != Value::MapK && slot->kind != Value::ListK) *slot = next_is_index ? Value::make_list() : Value::make_map();
         cur = slot;
     }
@@ -567,8 +582,8 @@ void assign(Value &root, const std::vector<PathElem> &path, const Value &value) 
 }  // namespace
 
 void apply_set(Value &values, const std::string &expr, bool force_string) {
-    for (const auto &kv : split_set(expr)) {
-        const std::string &val = kv.second;
+    for (auto &kv : split_set(expr)) {
+        std::string &val = kv.second;
         Value v;
         if (val.size() >= 2 && val.front() == '{' && val.back() == '}') {
             v = Value::make_list();
@@ -584,9 +599,9 @@ void apply_set(Value &values, const std::string &expr, bool force_string) {
                 }
             }
         } else {
-            v = set_typed(val, force_string);
+            v = set_typed(std::move(val), force_string);
         }
-        assign(values, split_key(kv.first), v);
+        assign(values, split_key(kv.first), std::move(v));
     }
 }
 
@@ -597,7 +612,7 @@ void apply_set_file(Value &values, const std::string &expr) {
 void apply_set_blob(Value &values, const std::string &key, std::string content) {
     Value v = Value::str(std::string());
     v.s = std::move(content);
-    assign(values, split_key(key), v);
+    assign(values, split_key(key), std::move(v));
 }
 
 // ============================================================================ coalesce
@@ -728,70 +743,130 @@ static int install_rank(const std::string &kind) {
 // behind the dashes belongs to the separator, and whatever follows the dashes on their line
 // starts the next document.  (Go's \s is [\t\n\f\r ].)
 static bool re_space(char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\f' || c == '\r'; }
-static std::vector<std::string> split_docs(const std::string &s) {
-    std::vector<std::string> docs;
-    size_t start = 0, i = 0;
-    for (;;) {
-        size_t ms, me;
-        if (i == 0 && s.compare(0, 3, "---") == 0) {
-            ms = 0;
-            me = 3;
-        } else {
-            const size_t p = s.find("\n---", i);
-            if (p == std::string::npos) break;
-            ms = p;
-            while (ms > i && re_space(s[ms - 1])) --ms;
-            me = p + 4;
+namespace {
+
+struct DocRef { const std::string *name; int rank; std::string kind; const char *p; size_t n; };
+
+bool uni_space(char c) { return is_ws(c) || c == '\v' || c == '\f'; }
+
+// Top-level "kind:" of a document head.
+std::string doc_kind(const char *d, size_t n) {
+    size_t i = 0;
+    while (i < n) {
+        const char *nl = static_cast<const char *>(memchr(d + i, '\n', n - i));
+        const size_t j = nl ? (size_t)(nl - d) : n;
+        if (j - i >= 5 && memcmp(d + i, "kind:", 5) == 0) {
+            size_t k = i + 5;
+            while (k < j && (d[k] == ' ' || d[k] == '\t')) ++k;
+            size_t e = k;
+            while (e < j && !is_ws(d[e]) && d[e] != '#') ++e;
+            std::string kind(d + k, e - k);
+            if (kind.size() >= 2 && (kind.front() == '"' || kind.front() == '\'')) kind = kind.substr(1, kind.size() - 2);
+            return kind;
         }
-        while (me < s.size() && re_space(s[me])) ++me;
-        docs.push_back(s.substr(start, ms - start));
-        start = i = me;
+        i = j + 1;
     }
-    docs.push_back(s.substr(start));
-    return docs;
+    return std::string();
 }
+
+// releaseutil.SortManifests over rendered files (sorted by path): documents as views into the
+// files' own text -- nothing is copied until the caller assembles its output.
+void sorted_docs(const std::vector<std::pair<const std::string *, const std::string *>> &files,
+                 std::vector<DocRef> *docs, const std::string **notes) {
+    for (const auto &f : files) {
+        const std::string &name = *f.first, &text = *f.second;
+        const size_t slash = name.find_last_of('/');
+        if (name.compare(slash == std::string::npos ? 0 : slash + 1, std::string::npos, "NOTES.txt") == 0) {
+            *notes = &text;
+            continue;
+        }
+        size_t a = 0, b = text.size();   // strings.TrimSpace
+        while (a < b && uni_space(text[a])) ++a;
+        while (b > a && uni_space(text[b - 1])) --b;
+        if (a == b) continue;
+        // SplitManifests' separator `(?:^|\s*\n)---\s*` over [a, b)
+        const char *t = text.data();
+        size_t start = a, i = a;
+        auto emit = [&](size_t lo, size_t hi) {
+            while (lo < hi && uni_space(t[lo])) ++lo;   // TrimLeftFunc(unicode.IsSpace)
+            if (lo == hi) return;
+            std::string kind = doc_kind(t + lo, hi - lo);
+            const int rank = install_rank(kind);
+            docs->push_back({&name, rank, std::move(kind), t + lo, hi - lo});
+        };
+        for (;;) {
+            size_t ms, me;
+            if (i == a && b - a >= 3 && memcmp(t + a, "---", 3) == 0) {
+                ms = a;
+                me = a + 3;
+            } else {
+                // next "\n---": hop from newline to newline (memchr runs at memory speed over the
+                // kilobytes of a Secret's payload, which hold no newline at all)
+                size_t p = i;
+                for (;;) {
+                    const char *nl = p + 4 <= b ? static_cast<const char *>(memchr(t + p, '\n', b - p - 3)) : nullptr;
+                    if (!nl) { p = std::string::npos; break; }
+                    p = (size_t)(nl - t);
+                    if (t[p + 1] == '-' && t[p + 2] == '-' && t[p + 3] == '-') break;
+                    ++p;
+                }
+                if (p == std::string::npos) break;
+                ms = p;
+                while (ms > i && re_space(t[ms - 1])) --ms;
+                me = p + 4;
+            }
+            while (me < b && re_space(t[me])) ++me;
+            emit(start, ms);
+            start = i = me;
+        }
+        emit(start, b);
+    }
+    std::stable_sort(docs->begin(), docs->end(), [](const DocRef &x, const DocRef &y) {
+        if (x.rank < 0 && y.rank < 0) return x.kind < y.kind;  // unknown kinds: alphabetical, stable within a kind
+        if (x.rank < 0) return false;
+        if (y.rank < 0) return true;
+        return x.rank < y.rank;
+    });
+}
+
+}  // namespace
 
 void split_manifests(const std::map<std::string, std::string> &files, std::vector<Manifest> *out, std::string *notes) {
     out->clear();
     notes->clear();
-    for (const auto &kv : files) {  // std::map: sorted by path, like Helm sorts file names
-        const std::string &name = kv.first;
-        std::string base = name.substr(name.find_last_of('/') + 1);
-        if (base == "NOTES.txt") { *notes = kv.second; continue; }
-        std::string t = trim_space(kv.second);
-        if (t.empty()) continue;
-        for (std::string doc : split_docs(t)) {
-            size_t a = 0;
-            while (a < doc.size() && is_ws(doc[a])) ++a;
-            doc.erase(0, a);
-            if (doc.empty()) continue;
-            // top-level "kind:" of the document head
-            std::string kind;
-            size_t i = 0;
-            while (i < doc.size()) {
-                size_t j = doc.find('\n', i);
-                if (j == std::string::npos) j = doc.size();
-                if (doc.compare(i, 5, "kind:") == 0) {
-                    size_t k = i + 5;
-                    while (k < j && (doc[k] == ' ' || doc[k] == '\t')) ++k;
-                    size_t e = k;
-                    while (e < j && !is_ws(doc[e]) && doc[e] != '#') ++e;
-                    kind = doc.substr(k, e - k);
-                    if (kind.size() >= 2 && (kind.front() == '"' || kind.front() == '\'')) kind = kind.substr(1, kind.size() - 2);
-                    break;
-                }
-                i = j + 1;
-            }
-            out->push_back({name, kind, doc});
-        }
+    std::vector<std::pair<const std::string *, const std::string *>> refs;
+    for (const auto &kv : files) refs.push_back({&kv.first, &kv.second});  // std::map: sorted by path, like Helm sorts file names
+    std::vector<DocRef> docs;
+    const std::string *n = nullptr;
+    sorted_docs(refs, &docs, &n);
+    if (n) *notes = *n;
+    for (const auto &d : docs) out->push_back({*d.name, d.kind, std::string(d.p, d.n)});
+}
+
+void frame_manifests(const std::vector<std::pair<const std::string *, const std::string *>> &files,
+                     std::string *manifest, std::string *notes) {
+    std::vector<DocRef> docs;
+    docs.reserve(files.size());
+    const std::string *n = nullptr;
+    sorted_docs(files, &docs, &n);
+    size_t total = 0;
+    for (const auto &d : docs) total += 14 + d.name->size() + 1 + d.n + 1;
+    manifest->clear();
+    manifest->reserve(total);
+    for (const auto &d : docs) {
+        manifest->append("---\n# Source: ", 14);
+        manifest->append(*d.name);
+        manifest->push_back('\n');
+        manifest->append(d.p, d.n);
+        manifest->push_back('\n');
     }
-    std::stable_sort(out->begin(), out->end(), [](const Manifest &a, const Manifest &b) {
-        int ra = install_rank(a.kind), rb = install_rank(b.kind);
-        if (ra < 0 && rb < 0) return a.kind < b.kind;  // unknown kinds: alphabetical, stable within a kind
-        if (ra < 0) return false;
-        if (rb < 0) return true;
-        return ra < rb;
-    });
+    notes->clear();
+    if (n) {
+        size_t a = 0, b = n->size();
+        while (a < b && uni_space((*n)[a])) ++a;
+        while (b > a && uni_space((*n)[b - 1])) --b;
+        notes->assign(*n, a, b - a);
+    }
 }
 
 }  // namespace chart

@@ -49,6 +49,11 @@ struct Manifest {
 void split_manifests(const std::map<std::string, std::string> &files, std::vector<Manifest> *out,
                      std::string *notes);
 
+// The same, straight to the `helm template` stream ("---\n# Source: <name>\n<doc>\n" per document
+// in install order) and the trimmed NOTES text.  `files`: (name, rendered text), sorted by name.
+void frame_manifests(const std::vector<std::pair<const std::string *, const std::string *>> &files,
+                     std::string *manifest, std::string *notes);
+
 std::string trim_space(const std::string &s);
 
 }  // namespace chart

@@ -7,6 +7,7 @@
 // (aziot-edge-runtime-config-secret.yaml:6, aziot-edge-vm-cloud-init-secret.yaml:6).
 #include "../../include/kvedge_b200.h"
 
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -36,6 +37,16 @@ struct kv_chart {
     Chart chart;
     TemplateSet ts;
     bool templates_have_sentinels = false;
+    // Everything of a render that does not depend on the release, built once at load: a fleet
+    // renders ONE chart thousands of times.
+    struct File {
+        std::string name;                         // "<chart>/templates/<file>"
+        const kvedge::tmpl::NodeList *nodes;      // its parsed body
+        Value tmpl;                               // .Template of this file
+    };
+    std::vector<File> files;                      // non-partial templates, sorted by name
+    Value chart_meta, caps;                       // .Chart, .Capabilities
+    bool defaults_have_sentinels = false;
 };
 
 struct kv_release {
@@ -115,7 +126,10 @@ std::string gpu_decode_one(const std::string &in) {
     return out;
 }
 
-Value merged_values(const kv_chart *c, const kv_overrides *ov) {
+// *user_sentinels: whether any value the caller supplied holds a placeholder byte (the chart's
+// own defaults were checked when it was loaded).
+Value merged_values(const kv_chart *c, const kv_overrides *ov, bool *user_sentinels = nullptr) {
+    if (user_sentinels) *user_sentinels = false;
     if (!ov) return kvedge::tmpl::deep_copy(c->chart.values);
     // Helm collects the flags into a map of their own and then slides the chart's defaults
     // under it (chartutil.CoalesceValues): null deletes a default, lists are not patched.
@@ -126,20 +140,14 @@ Value merged_values(const kv_chart *c, const kv_overrides *ov) {
     for (int i = 0; i < ov->n_blob; ++i)
         kvedge::chart::apply_set_blob(vals, ov->blob_keys[i],
                                       std::string(reinterpret_cast<const char *>(ov->blob_data[i]), ov->blob_len[i]));
+    if (user_sentinels) *user_sentinels = value_has_sentinels(vals);
     return kvedge::chart::coalesce_values(c->chart.values, std::move(vals));
 }
 
-// Render every non-partial file of the chart; keys are "<chart>/templates/<file>".
-std::map<std::string, std::string> render_files(const kv_chart *c, const Value &vals, const char *release,
-                                                const char *ns, bool defer, std::vector<Pending> *pending) {
+// What does not depend on the release: .Chart, .Capabilities, and per file its name, parsed body
+// and .Template.
+void prepare_chart(kv_chart *c) {
     const std::string prefix = c->chart.name() + "/";
-    Value rel = Value::make_map();
-    (*rel.map)["Name"] = Value::str(release ? release : "release-name");
-    (*rel.map)["Namespace"] = Value::str(ns ? ns : "default");
-    (*rel.map)["IsUpgrade"] = Value::boolean(false);
-    (*rel.map)["IsInstall"] = Value::boolean(true);
-    (*rel.map)["Revision"] = Value::integer(1);
-    (*rel.map)["Service"] = Value::str("Helm");
     Value caps = Value::make_map();
     Value kube = Value::make_map();
     (*kube.map)["Version"] = Value::str("v1.20.0");
@@ -149,46 +157,67 @@ std::map<std::string, std::string> render_files(const kv_chart *c, const Value &
     Value hv = Value::make_map();
     (*hv.map)["Version"] = Value::str("v3.7.0");
     (*caps.map)["HelmVersion"] = hv;
-    Value chart_meta = chart_struct(c->chart.metadata);
+    c->caps = caps;
+    c->chart_meta = chart_struct(c->chart.metadata);
+    c->defaults_have_sentinels = value_has_sentinels(c->chart.values);
+    for (const auto &t : c->chart.templates) {
+        const std::string &rel_path = t.first;
+        const std::string base = rel_path.substr(rel_path.find_last_of('/') + 1);
+        if (!base.empty() && base[0] == '_') continue;
+        kv_chart::File f;
+        f.name = prefix + rel_path;
+        f.nodes = c->ts.find(f.name);
+        f.tmpl = Value::make_map();
+        (*f.tmpl.map)["Name"] = Value::str(f.name);
+        (*f.tmpl.map)["BasePath"] = Value::str(prefix + "templates");
+        c->files.push_back(std::move(f));
+    }
+    std::sort(c->files.begin(), c->files.end(), [](const kv_chart::File &a, const kv_chart::File &b) { return a.name < b.name; });
+}
+
+// Render every non-partial file of the chart, in name order; rendered[k] belongs to c->files[k].
+void render_files(const kv_chart *c, const Value &vals, const char *release, const char *ns, bool defer,
+                  std::vector<Pending> *pending, std::vector<std::string> *rendered) {
+    Value rel = Value::make_map();
+    (*rel.map)["Name"] = Value::str(release ? release : "release-name");
+    (*rel.map)["Namespace"] = Value::str(ns ? ns : "default");
+    (*rel.map)["IsUpgrade"] = Value::boolean(false);
+    (*rel.map)["IsInstall"] = Value::boolean(true);
+    (*rel.map)["Revision"] = Value::integer(1);
+    (*rel.map)["Service"] = Value::str("Helm");
+    Value top = Value::make_map();
+    (*top.map)["Values"] = vals;
+    (*top.map)["Chart"] = c->chart_meta;
+    (*top.map)["Release"] = rel;
+    (*top.map)["Capabilities"] = c->caps;
+    Value &tmpl_slot = (*top.map)["Template"];
 
     TemplateSet::ExecOptions opt;
     opt.defer_b64 = defer;
     opt.pending = pending;
     opt.encode = gpu_encode_one;
     opt.decode = gpu_decode_one;
-    std::map<std::string, std::string> out;
-    for (const auto &t : c->chart.templates) {
-        const std::string &rel_path = t.first;
-        std::string base = rel_path.substr(rel_path.find_last_of('/') + 1);
-        if (!base.empty() && base[0] == '_') continue;
-        Value top = Value::make_map();
-        (*top.map)["Values"] = vals;
-        (*top.map)["Chart"] = chart_meta;
-        (*top.map)["Release"] = rel;
-        Value tv = Value::make_map();
-        (*tv.map)["Name"] = Value::str(prefix + rel_path);
-        (*tv.map)["BasePath"] = Value::str(prefix + "templates");
-        (*top.map)["Template"] = tv;
-        (*top.map)["Capabilities"] = caps;
-        std::string rendered;
+    rendered->assign(c->files.size(), std::string());
+    for (size_t k = 0; k < c->files.size(); ++k) {
+        const kv_chart::File &f = c->files[k];
+        tmpl_slot = f.tmpl;
+        std::string &out = (*rendered)[k];
+        out.reserve(4096);
         try {
-            rendered = c->ts.execute(prefix + rel_path, top, opt);
+            c->ts.execute_into(*f.nodes, top, opt, out);
         } catch (const kvedge::tmpl::Error &e) {
-            throw kvedge::tmpl::Error("template: " + prefix + rel_path + ": " + e.what());
+            throw kvedge::tmpl::Error("template: " + f.name + ": " + e.what());
         }
-        replace_all_inplace(rendered, "<no value>", "");  // missingkey=zero, non-strict
-        out[prefix + rel_path] = rendered;
+        if (out.find("<no value>") != std::string::npos)
+            replace_all_inplace(out, "<no value>", "");  // missingkey=zero, non-strict
     }
-    return out;
 }
 
-void frame(const std::map<std::string, std::string> &files, std::string *manifest, std::string *notes) {
-    std::vector<Manifest> ms;
-    std::string raw_notes;
-    kvedge::chart::split_manifests(files, &ms, &raw_notes);
-    manifest->clear();
-    for (const auto &m : ms) *manifest += "---\n# Source: " + m.name + "\n" + m.content + "\n";
-    *notes = kvedge::chart::trim_space(raw_notes);
+void frame(const kv_chart *c, const std::vector<std::string> &rendered, std::string *manifest, std::string *notes) {
+    std::vector<std::pair<const std::string *, const std::string *>> files;
+    files.reserve(rendered.size());
+    for (size_t k = 0; k < rendered.size(); ++k) files.push_back({&c->files[k].name, &rendered[k]});
+    kvedge::chart::frame_manifests(files, manifest, notes);
 }
 
 // Write every filled encoding over its placeholder (found by its 4 id bytes).
@@ -250,10 +279,12 @@ void parallel_for(int n, F fn) {
 int plan_release(const kv_chart *c, const char *release, const char *ns, const kv_overrides *ov, bool defer,
                  kv_release **out) {
     std::unique_ptr<kv_release> r(new kv_release);
-    Value vals = merged_values(c, ov);
-    bool can_defer = defer && !c->templates_have_sentinels && !value_has_sentinels(vals);
-    auto files = render_files(c, vals, release, ns, can_defer, &r->pending);
-    frame(files, &r->manifest, &r->notes);
+    bool user_sentinels = false;
+    Value vals = merged_values(c, ov, &user_sentinels);
+    const bool can_defer = defer && !c->templates_have_sentinels && !c->defaults_have_sentinels && !user_sentinels;
+    std::vector<std::string> rendered;
+    render_files(c, vals, release, ns, can_defer, &r->pending, &rendered);
+    frame(c, rendered, &r->manifest, &r->notes);
     r->filled.assign(r->pending.size(), std::string());
     *out = r.release();
     return KV_OK;
@@ -273,6 +304,7 @@ int kv_chart_load(const char *chart_dir, kv_chart **out) {
             c->ts.parse(prefix + t.first, t.second);
             if (TemplateSet::has_sentinel_bytes(t.second)) c->templates_have_sentinels = true;
         }
+        prepare_chart(c.get());
         *out = c.release();
         return KV_OK;
     } catch (const std::exception &e) {
@@ -565,10 +597,14 @@ int kv_helm_lint(const char *chart_dir, const kv_overrides *overrides, int *ok, 
             msgs.push_back("[ERROR] Chart.yaml: chart type is not valid in apiVersion 'v2'. It must be 'application' or 'library'");
         if (get("icon").empty()) msgs.push_back("[INFO] Chart.yaml: icon is recommended");
         try {
-            Value vals = merged_values(c, overrides);
+            bool user_sentinels = false;
+            Value vals = merged_values(c, overrides, &user_sentinels);
             std::vector<Pending> pending;
-            bool defer = !c->templates_have_sentinels && !value_has_sentinels(vals);
-            auto files = render_files(c, vals, "test-release", "default", defer, &pending);
+            const bool defer = !c->templates_have_sentinels && !c->defaults_have_sentinels && !user_sentinels;
+            std::vector<std::string> rendered;
+            render_files(c, vals, "test-release", "default", defer, &pending, &rendered);
+            std::map<std::string, std::string> files;
+            for (size_t k = 0; k < rendered.size(); ++k) files[c->files[k].name] = rendered[k];
             std::vector<Manifest> ms;
             std::string notes;
             kvedge::chart::split_manifests(files, &ms, &notes);

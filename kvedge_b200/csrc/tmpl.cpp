@@ -8,6 +8,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
+#ifdef __SSE2__
+#include <emmintrin.h>
+#endif
 
 namespace kvedge {
 namespace tmpl {
@@ -199,19 +203,47 @@ std::string go_quote(const std::string &s) {
 }
 
 // ============================================================================ AST
+// Functions, resolved to an id when a template is parsed.
+enum Fn : int {
+    F_NONE = -1, F_include, F_default, F_trunc, F_trimSuffix, F_trimPrefix, F_replace, F_quote, F_squote, F_indent,
+    F_nindent, F_b64enc, F_b64dec, F_eq, F_ne, F_lt, F_le, F_gt, F_ge, F_not, F_printf, F_print, F_println, F_len,
+    F_empty, F_required, F_lower, F_upper, F_trim, F_toString, F_hasKey, F_ternary, F_cat, F_contains, F_hasPrefix,
+    F_hasSuffix, F_repeat, F_and, F_or
+};
+static int fn_id(const std::string &name) {
+    static const std::map<std::string, int> ids = {
+        {"include", F_include}, {"default", F_default}, {"trunc", F_trunc}, {"trimSuffix", F_trimSuffix},
+        {"trimPrefix", F_trimPrefix}, {"replace", F_replace}, {"quote", F_quote}, {"squote", F_squote},
+        {"indent", F_indent}, {"nindent", F_nindent}, {"b64enc", F_b64enc}, {"b64dec", F_b64dec}, {"eq", F_eq},
+        {"ne", F_ne}, {"lt", F_lt}, {"le", F_le}, {"gt", F_gt}, {"ge", F_ge}, {"not", F_not}, {"printf", F_printf},
+        {"print", F_print}, {"println", F_println}, {"len", F_len}, {"empty", F_empty}, {"required", F_required},
+        {"lower", F_lower}, {"upper", F_upper}, {"trim", F_trim}, {"toString", F_toString}, {"hasKey", F_hasKey},
+        {"ternary", F_ternary}, {"cat", F_cat}, {"contains", F_contains}, {"hasPrefix", F_hasPrefix},
+        {"hasSuffix", F_hasSuffix}, {"repeat", F_repeat}, {"and", F_and}, {"or", F_or}};
+    auto it = ids.find(name);
+    return it == ids.end() ? F_NONE : it->second;
+}
+
 struct Operand {
     enum Kind { Dot, Field, Var, Str, Num, BoolK, NilK, Ident, Paren } kind = Dot;
     std::string text;                 // Var name / Ident / Str payload
+    int fn = F_NONE;                  // Ident: the function's id (F_NONE: unknown, an error when it runs)
+    Value lit;                        // Str / Num / Bool / nil literal, built once
     Value num;                        // Num / Bool literal
     std::vector<std::string> fields;  // .A.B chain
     std::shared_ptr<struct Pipeline> paren;
 };
-struct Command { std::vector<Operand> args; };
+struct Command {
+    std::vector<Operand> args;
+    size_t n_computed = 0;  // arguments that are parenthesised pipelines or bare function names
+};
 struct Pipeline {
     std::vector<Command> cmds;
     std::string decl;       // "$x" when the pipeline declares / assigns a variable
     bool is_assign = false;
+    bool defer_candidate = false;   // `<two or more commands> | b64enc`, no variable: may stay pending
 };
+struct Var { const std::string *name; Value v; };
 struct Node {
     enum Kind { Text, Action, If, With, Range, Template } kind = Text;
     std::string text;                 // Text payload / Template name
@@ -510,6 +542,9 @@ struct PipeParser {
             p->cmds.push_back(command(end));
         }
         if (peek().kind != end) throw Error(where + ": unexpected \"" + peek().text + "\" in pipeline");
+        const Command &last = p->cmds.back();
+        p->defer_candidate = p->decl.empty() && p->cmds.size() >= 2 && last.args.size() == 1 &&
+                             last.args[0].kind == Operand::Ident && last.args[0].fn == F_b64enc;
         return p;
     }
     Command command(Tok::Kind end) {
@@ -520,6 +555,8 @@ struct PipeParser {
             c.args.push_back(operand());
         }
         if (c.args.empty()) throw Error(where + ": missing value for command");
+        for (size_t k = 1; k < c.args.size(); ++k)
+            if (c.args[k].kind == Operand::Paren || c.args[k].kind == Operand::Ident) ++c.n_computed;
         return c;
     }
     Operand operand() {
@@ -577,6 +614,9 @@ struct PipeParser {
         default:
             throw Error(where + ": unexpected \"" + t.text + "\" in operand");
         }
+        if (op.kind == Operand::Str) op.lit = Value::str(op.text);
+        else if (op.kind == Operand::Num || op.kind == Operand::BoolK) op.lit = op.num;
+        else if (op.kind == Operand::Ident) op.fn = fn_id(op.text);
         return op;
     }
 };
@@ -767,7 +807,17 @@ const char *basic_kind(const Value &v) {
     }
 }
 
-bool eq_fn(const std::vector<Value> &a) {
+// A function's arguments: pointers at values that live elsewhere (the value tree, literals of
+// the AST, temporaries of the caller).
+struct ArgView {
+    const Value *const *p;
+    size_t n;
+    const Value &operator[](size_t i) const { return *p[i]; }
+    size_t size() const { return n; }
+    bool empty() const { return n == 0; }
+};
+
+bool eq_fn(const ArgView &a) {
     if (a.size() < 2) throw Error("missing argument for comparison");
     std::string ka = basic_kind(a[0]);
     for (size_t k = 1; k < a.size(); ++k) {
@@ -788,7 +838,7 @@ bool eq_fn(const std::vector<Value> &a) {
     return false;
 }
 
-bool cmp_fn(const std::string &op, const Value &a, const Value &b) {
+bool cmp_fn(int op, const Value &a, const Value &b) {
     std::string ka = basic_kind(a), kb = basic_kind(b);
     if (ka != kb) throw Error("incompatible types for comparison");
     int c;
@@ -796,9 +846,9 @@ bool cmp_fn(const std::string &op, const Value &a, const Value &b) {
     else if (ka == "float") c = a.f < b.f ? -1 : a.f > b.f;
     else if (ka == "string") c = a.s.compare(b.s) < 0 ? -1 : a.s.compare(b.s) > 0;
     else throw Error("invalid type for comparison");
-    if (op == "lt") return c < 0;
-    if (op == "le") return c <= 0;
-    if (op == "gt") return c > 0;
+    if (op == F_lt) return c < 0;
+    if (op == F_le) return c <= 0;
+    if (op == F_gt) return c > 0;
     return c >= 0;
 }
 
@@ -821,7 +871,7 @@ const std::string &string_arg(const Value &v, const std::string &fn) {
     throw Error("executing at <" + fn + ">: wrong type for value; expected string; got " + go_typename(v));
 }
 
-std::string sprintf_fn(const std::vector<Value> &a) {
+std::string sprintf_fn(const ArgView &a) {
     if (a.empty()) throw Error("wrong number of args for printf: want at least 1 got 0");
     std::string fmt = strval(a[0]), o;
     size_t ai = 1;
@@ -865,36 +915,44 @@ std::string ascii_map(const std::string &s, int (*f)(int)) {
 }  // namespace
 
 // ============================================================================ executor
+// One render = thousands of these calls across a fleet, so the executor is written to touch the
+// allocator as little as it can: operands that name a value (.Values.x, $v, literals) are passed
+// around as POINTERS into the value tree, never copied; functions are dispatched on an id
+// resolved at parse time; arguments sit in a small array on the stack; variables live in one flat
+// stack; `include` captures into a buffer whose capacity is reused.
 struct Exec {
     const TemplateSet &ts;
     const TemplateSet::ExecOptions &opt;
     int capture_depth = 0;  // > 0 while executing inside include (output is captured as a value)
 
-    using Scopes = std::vector<std::map<std::string, Value>>;
+    // live variables, innermost last.  A deque: references to its elements (a `$x` handed to a
+    // function, the dot of a `with $x`) stay valid while later variables come and go.
+    std::deque<Var> &vars;
+    std::vector<std::string> &capture_pool;   // spare buffers for include
+    size_t frame_base = 0;      // variables below this belong to the caller of include/template
 
-    Value lookup_var(const std::string &name, Scopes &sc) {
-        for (size_t k = sc.size(); k-- > 0;) {
-            auto it = sc[k].find(name);
-            if (it != sc[k].end()) return it->second;
-        }
+    static const std::string &dollar() { static const std::string d = "$"; return d; }
+    static const Value &no_value() { static const Value v = Value::novalue(); return v; }
+
+    const Value *lookup_var(const std::string &name) const {
+        for (size_t k = vars.size(); k-- > frame_base;)
+            if (*vars[k].name == name) return &vars[k].v;
         throw Error("undefined variable \"" + name + "\"");
     }
 
-    Value field_chain(Value v, const std::vector<std::string> &fields) {
+    const Value *field_ref(const Value *v, const std::vector<std::string> &fields) const {
         for (const auto &f : fields) {
-            if (v.kind == Value::StructK) {
-                auto it = v.map->find(f);
-                if (it == v.map->end()) throw Error("can't evaluate field " + f + " in type " + v.s);
-                Value nx = it->second;
-                v = nx;
-            } else if (v.kind == Value::MapK) {
-                auto it = v.map->find(f);
-                Value nx = it == v.map->end() ? Value::novalue() : it->second;
-                v = nx;
-            } else if (v.is_nilish()) {
+            if (v->kind == Value::StructK) {
+                auto it = v->map->find(f);
+                if (it == v->map->end()) throw Error("can't evaluate field " + f + " in type " + v->s);
+                v = &it->second;
+            } else if (v->kind == Value::MapK) {
+                auto it = v->map->find(f);
+                v = it == v->map->end() ? &no_value() : &it->second;
+            } else if (v->is_nilish()) {
                 throw Error("nil pointer evaluating interface {}." + f);
             } else {
-                throw Error("can't evaluate field " + f + " in type " + go_typename(v));
+                throw Error("can't evaluate field " + f + " in type " + go_typename(*v));
             }
         }
         return v;
@@ -906,84 +964,114 @@ struct Exec {
         return opt.encode(s);
     }
 
-    Value call(const std::string &fn, std::vector<Value> &a, const Value &dot) {
-        (void)dot;
+    // Run a named template with `data` as dot and `$`, appending to out.
+    void run_template(const std::string &tname, const Value &data, std::string &out) {
+        auto it = ts.templates_.find(tname);
+        if (it == ts.templates_.end()) throw Error("template \"" + tname + "\" not defined");
+        const size_t saved_base = frame_base, saved_size = vars.size();
+        frame_base = saved_size;
+        vars.push_back({&dollar(), data});
+        try {
+            exec_list(it->second, vars[saved_size].v, out);
+        } catch (...) {
+            vars.resize(saved_size);
+            frame_base = saved_base;
+            throw;
+        }
+        vars.resize(saved_size);
+        frame_base = saved_base;
+    }
+
+    Value call(int fn, const std::string &fname, const ArgView &a) {
         auto need = [&](size_t n) {
             if (a.size() != n)
-                throw Error("wrong number of args for " + fn + ": want " + std::to_string(n) + " got " + std::to_string(a.size()));
+                throw Error("wrong number of args for " + fname + ": want " + std::to_string(n) + " got " + std::to_string(a.size()));
         };
         auto empty = [](const Value &v) { return !truth(v); };
-        if (fn == "include") {
+        switch (fn) {
+        case F_include: {
             need(2);
-            std::string tname = strval(a[0]);
-            auto it = ts.templates_.find(tname);
-            if (it == ts.templates_.end()) throw Error("template \"" + tname + "\" not defined");
-            std::string out;
-            Scopes sc(1);
-            sc[0]["$"] = a[1];
+            std::string buf;
+            if (!capture_pool.empty()) { buf = std::move(capture_pool.back()); capture_pool.pop_back(); buf.clear(); }
             ++capture_depth;
-            exec_list(it->second, a[1], sc, out);
+            try {
+                run_template(strval(a[0]), a[1], buf);
+            } catch (...) {
+                --capture_depth;
+                throw;
+            }
             --capture_depth;
-            return Value::str(out);
+            return Value::str(std::move(buf));
         }
-        if (fn == "default") {
+        case F_default:
             if (a.empty()) throw Error("wrong number of args for default");
             if (a.size() < 2 || empty(a[1])) return a[0];
             return a[1];
-        }
-        if (fn == "trunc") {
+        case F_trunc: {
             need(2);
             int64_t c = to_int(a[0]);
-            std::string s = string_arg(a[1], fn);
+            const std::string &s = string_arg(a[1], fname);
             if (c < 0 && (int64_t)s.size() + c > 0) return Value::str(s.substr((size_t)((int64_t)s.size() + c)));
             if (c >= 0 && (int64_t)s.size() > c) return Value::str(s.substr(0, (size_t)c));
             return Value::str(s);
         }
-        if (fn == "trimSuffix") {
+        case F_trimSuffix: {
             need(2);
-            std::string suf = string_arg(a[0], fn), s = string_arg(a[1], fn);
+            const std::string &suf = string_arg(a[0], fname);
+            std::string s = string_arg(a[1], fname);
             if (!suf.empty() && s.size() >= suf.size() && s.compare(s.size() - suf.size(), suf.size(), suf) == 0)
                 s.erase(s.size() - suf.size());
-            return Value::str(s);
+            return Value::str(std::move(s));
         }
-        if (fn == "trimPrefix") {
+        case F_trimPrefix: {
             need(2);
-            std::string pre = string_arg(a[0], fn), s = string_arg(a[1], fn);
+            const std::string &pre = string_arg(a[0], fname);
+            std::string s = string_arg(a[1], fname);
             if (!pre.empty() && s.compare(0, pre.size(), pre) == 0) s.erase(0, pre.size());
-            return Value::str(s);
+            return Value::str(std::move(s));
         }
-        if (fn == "replace") { need(3); return Value::str(replace_all(string_arg(a[2], fn), string_arg(a[0], fn), string_arg(a[1], fn))); }
-        if (fn == "quote" || fn == "squote") {
+        case F_replace:
+            need(3);
+            return Value::str(replace_all(string_arg(a[2], fname), string_arg(a[0], fname), string_arg(a[1], fname)));
+        case F_quote: case F_squote: {
             std::string o;
             bool first = true;
-            for (const auto &x : a) {
+            for (size_t k = 0; k < a.size(); ++k) {
+                const Value &x = a[k];
                 if (x.is_nilish()) continue;
                 if (!first) o += " ";
                 first = false;
-                o += fn == "quote" ? go_quote(strval(x)) : "'" + go_print(x) + "'";
+                o += fn == F_quote ? go_quote(strval(x)) : "'" + go_print(x) + "'";
             }
-            return Value::str(o);
+            return Value::str(std::move(o));
         }
-        if (fn == "indent" || fn == "nindent") {
+        case F_indent: case F_nindent: {
             need(2);
-            std::string pad((size_t)std::max<int64_t>(0, to_int(a[0])), ' ');
-            std::string o = pad + replace_all(string_arg(a[1], fn), "\n", "\n" + pad);
-            return Value::str(fn == "nindent" ? "\n" + o : o);
+            const std::string pad((size_t)std::max<int64_t>(0, to_int(a[0])), ' ');
+            const std::string &s = string_arg(a[1], fname);
+            std::string o;
+            o.reserve(s.size() + pad.size() * 8 + 1);
+            if (fn == F_nindent) o.push_back('\n');
+            o += pad;
+            for (char ch : s) {
+                o.push_back(ch);
+                if (ch == '\n') o += pad;
+            }
+            return Value::str(std::move(o));
         }
-        if (fn == "b64enc") { need(1); return Value::str(encode_now(string_arg(a[0], fn))); }
-        if (fn == "b64dec") {
+        case F_b64enc: need(1); return Value::str(encode_now(string_arg(a[0], fname)));
+        case F_b64dec:
             need(1);
             if (!opt.decode) throw Error("b64dec: no decoder attached (GPU required)");
-            return Value::str(opt.decode(string_arg(a[0], fn)));
-        }
-        if (fn == "eq") return Value::boolean(eq_fn(a));
-        if (fn == "ne") { need(2); return Value::boolean(!eq_fn(a)); }
-        if (fn == "lt" || fn == "le" || fn == "gt" || fn == "ge") { need(2); return Value::boolean(cmp_fn(fn, a[0], a[1])); }
-        if (fn == "not") { need(1); return Value::boolean(!truth(a[0])); }
-        if (fn == "printf") return Value::str(sprintf_fn(a));
-        if (fn == "print" || fn == "println") {
+            return Value::str(opt.decode(string_arg(a[0], fname)));
+        case F_eq: return Value::boolean(eq_fn(a));
+        case F_ne: need(2); return Value::boolean(!eq_fn(a));
+        case F_lt: case F_le: case F_gt: case F_ge: need(2); return Value::boolean(cmp_fn(fn, a[0], a[1]));
+        case F_not: need(1); return Value::boolean(!truth(a[0]));
+        case F_printf: return Value::str(sprintf_fn(a));
+        case F_print: case F_println: {
             std::string o;
-            if (fn == "println") {
+            if (fn == F_println) {
                 for (size_t k = 0; k < a.size(); ++k) { if (k) o += " "; o += go_print(a[k]); }
                 return Value::str(o + "\n");
             }
@@ -994,148 +1082,168 @@ struct Exec {
                 o += go_print(a[k]);
                 prev_str = is_s;
             }
-            return Value::str(o);
+            return Value::str(std::move(o));
         }
-        if (fn == "len") {
+        case F_len:
             need(1);
             if (a[0].kind == Value::String) return Value::integer((int64_t)a[0].s.size());
             if (a[0].kind == Value::ListK) return Value::integer((int64_t)a[0].list->size());
             if (a[0].kind == Value::MapK) return Value::integer((int64_t)a[0].map->size());
             throw Error("len of type " + go_typename(a[0]));
-        }
-        if (fn == "empty") { need(1); return Value::boolean(empty(a[0])); }
-        if (fn == "required") {
+        case F_empty: need(1); return Value::boolean(empty(a[0]));
+        case F_required:
             need(2);
             if (a[1].is_nilish() || (a[1].kind == Value::String && a[1].s.empty())) throw Error(strval(a[0]));
             return a[1];
-        }
-        if (fn == "lower") { need(1); return Value::str(ascii_map(string_arg(a[0], fn), ::tolower)); }
-        if (fn == "upper") { need(1); return Value::str(ascii_map(string_arg(a[0], fn), ::toupper)); }
-        if (fn == "trim") {
+        case F_lower: need(1); return Value::str(ascii_map(string_arg(a[0], fname), ::tolower));
+        case F_upper: need(1); return Value::str(ascii_map(string_arg(a[0], fname), ::toupper));
+        case F_trim: {
             need(1);
-            std::string s = string_arg(a[0], fn);
+            const std::string &s = string_arg(a[0], fname);
             size_t x = 0, y = s.size();
             while (x < y && (is_space(s[x]) || s[x] == '\v' || s[x] == '\f')) ++x;
             while (y > x && (is_space(s[y - 1]) || s[y - 1] == '\v' || s[y - 1] == '\f')) --y;
             return Value::str(s.substr(x, y - x));
         }
-        if (fn == "toString") { need(1); return Value::str(strval(a[0])); }
-        if (fn == "hasKey") {
+        case F_toString: need(1); return Value::str(strval(a[0]));
+        case F_hasKey:
             need(2);
             return Value::boolean(a[0].kind == Value::MapK && a[0].map->count(strval(a[1])) != 0);
-        }
-        if (fn == "ternary") { need(3); return truth(a[2]) ? a[0] : a[1]; }
-        if (fn == "cat") {
+        case F_ternary: need(3); return truth(a[2]) ? a[0] : a[1];
+        case F_cat: {
             std::string o;
             bool first = true;
-            for (const auto &x : a) {
-                if (x.is_nilish()) continue;
+            for (size_t k = 0; k < a.size(); ++k) {
+                if (a[k].is_nilish()) continue;
                 if (!first) o += " ";
                 first = false;
-                o += strval(x);
+                o += strval(a[k]);
             }
-            return Value::str(o);
+            return Value::str(std::move(o));
         }
-        if (fn == "contains") { need(2); return Value::boolean(string_arg(a[1], fn).find(string_arg(a[0], fn)) != std::string::npos); }
-        if (fn == "hasPrefix") { need(2); std::string p = string_arg(a[0], fn), s = string_arg(a[1], fn); return Value::boolean(s.compare(0, p.size(), p) == 0); }
-        if (fn == "hasSuffix") {
+        case F_contains: need(2); return Value::boolean(string_arg(a[1], fname).find(string_arg(a[0], fname)) != std::string::npos);
+        case F_hasPrefix: {
             need(2);
-            std::string p = string_arg(a[0], fn), s = string_arg(a[1], fn);
+            const std::string &p = string_arg(a[0], fname), &s = string_arg(a[1], fname);
+            return Value::boolean(s.compare(0, p.size(), p) == 0);
+        }
+        case F_hasSuffix: {
+            need(2);
+            const std::string &p = string_arg(a[0], fname), &s = string_arg(a[1], fname);
             return Value::boolean(s.size() >= p.size() && s.compare(s.size() - p.size(), p.size(), p) == 0);
         }
-        if (fn == "repeat") {
+        case F_repeat: {
             need(2);
-            std::string o, s = string_arg(a[1], fn);
+            std::string o;
+            const std::string &s = string_arg(a[1], fname);
             for (int64_t k = 0; k < to_int(a[0]); ++k) o += s;
-            return Value::str(o);
+            return Value::str(std::move(o));
         }
-        throw Error("function \"" + fn + "\" not defined");
+        default: break;
+        }
+        throw Error("function \"" + fname + "\" not defined");
     }
 
-    Value eval_operand(const Operand &op, const Value &dot, Scopes &sc) {
+    // The value an operand names: a pointer into the value tree or at a literal of the AST, or,
+    // for a computed operand, at `tmp`, which then holds the result.
+    const Value *eval_operand(const Operand &op, const Value &dot, Value &tmp) {
         switch (op.kind) {
-        case Operand::Dot: return dot;
-        case Operand::Field: return field_chain(dot, op.fields);
-        case Operand::Var: return field_chain(lookup_var(op.text, sc), op.fields);
-        case Operand::Str: return Value::str(op.text);
-        case Operand::Num: case Operand::BoolK: return op.num;
-        case Operand::NilK: return Value::nil();
-        case Operand::Paren: return field_chain(eval_pipe(*op.paren, dot, sc), op.fields);
-        case Operand::Ident: {
-            std::vector<Value> none;
-            return call(op.text, none, dot);
-        }
+        case Operand::Dot: return &dot;
+        case Operand::Field: return field_ref(&dot, op.fields);
+        case Operand::Var: return field_ref(lookup_var(op.text), op.fields);
+        case Operand::Str: case Operand::Num: case Operand::BoolK: case Operand::NilK: return &op.lit;
+        case Operand::Paren:
+            tmp = eval_pipe_value(*op.paren, dot);
+            return field_ref(&tmp, op.fields);
+        case Operand::Ident:
+            tmp = call(op.fn, op.text, ArgView{nullptr, 0});
+            return &tmp;
         }
         throw Error("bad operand");
     }
 
-    Value eval_cmd(const Command &cmd, const Value &dot, Scopes &sc, const Value *piped) {
+    static constexpr size_t kMaxArgs = 16;
+
+    // One command of a pipeline; `piped` is the previous command's value (the last argument).
+    // Returns where the result is: in the tree, in the AST, or in `result`.
+    const Value *eval_cmd(const Command &cmd, const Value &dot, const Value *piped, Value &result) {
         const Operand &first = cmd.args[0];
-        if (first.kind == Operand::Ident) {
-            const std::string &fn = first.text;
-            if (fn == "and" || fn == "or") {
-                size_t n_args = cmd.args.size() - 1 + (piped ? 1 : 0);
-                if (n_args == 0) throw Error("wrong number of args for " + fn);
-                Value res;
-                for (size_t k = 0; k < n_args; ++k) {
-                    res = k + 1 < cmd.args.size() ? eval_operand(cmd.args[k + 1], dot, sc) : *piped;
-                    if ((fn == "and") != truth(res)) return res;
-                }
-                return res;
-            }
-            std::vector<Value> args;
-            for (size_t k = 1; k < cmd.args.size(); ++k) args.push_back(eval_operand(cmd.args[k], dot, sc));
-            if (piped) args.push_back(*piped);
-            return call(fn, args, dot);
+        if (first.kind != Operand::Ident) {
+            if (cmd.args.size() > 1 || piped) throw Error("can't give argument to non-function");
+            return eval_operand(first, dot, result);
         }
-        if (cmd.args.size() > 1 || piped) throw Error("can't give argument to non-function");
-        return eval_operand(first, dot, sc);
+        const size_t n_args = cmd.args.size() - 1 + (piped ? 1 : 0);
+        if (first.fn == F_and || first.fn == F_or) {
+            if (n_args == 0) throw Error("wrong number of args for " + first.text);
+            const Value *res = nullptr;
+            Value tmp;
+            for (size_t k = 0; k < n_args; ++k) {
+                res = k + 1 < cmd.args.size() ? eval_operand(cmd.args[k + 1], dot, tmp) : piped;
+                if ((first.fn == F_and) != truth(*res)) break;
+            }
+            if (res == &tmp) { result = std::move(tmp); return &result; }
+            return res;
+        }
+        if (n_args > kMaxArgs) throw Error("too many arguments to " + first.text);
+        const Value *argv[kMaxArgs];
+        // computed operands (parenthesised pipelines, bare function names) need a home; they are rare
+        std::unique_ptr<Value[]> tmps(cmd.n_computed ? new Value[cmd.n_computed] : nullptr);
+        size_t t = 0, n = 0;
+        for (size_t k = 1; k < cmd.args.size(); ++k) {
+            const Operand &op = cmd.args[k];
+            const bool computed = op.kind == Operand::Paren || op.kind == Operand::Ident;
+            argv[n++] = computed ? eval_operand(op, dot, tmps[t++]) : eval_operand(op, dot, result);
+        }
+        if (piped) argv[n++] = piped;
+        result = call(first.fn, first.text, ArgView{argv, n});
+        return &result;
     }
 
-    // Evaluate the first `upto` commands of a pipeline.
-    Value eval_pipe_prefix(const Pipeline &p, size_t upto, const Value &dot, Scopes &sc) {
-        Value v;
-        bool has = false;
-        for (size_t k = 0; k < upto; ++k) {
-            Value nv = eval_cmd(p.cmds[k], dot, sc, has ? &v : nullptr);
-            v = nv;
-            has = true;
-        }
+    // The first `upto` commands of a pipeline.  h0/h1 are two holders the commands' results
+    // alternate between (a command reads the previous holder while writing the other).
+    const Value *eval_pipe_prefix(const Pipeline &p, size_t upto, const Value &dot, Value &h0, Value &h1) {
+        const Value *v = nullptr;
+        for (size_t k = 0; k < upto; ++k) v = eval_cmd(p.cmds[k], dot, v, (k & 1) ? h1 : h0);
         return v;
     }
 
-    Value eval_pipe(const Pipeline &p, const Value &dot, Scopes &sc) {
-        Value v = eval_pipe_prefix(p, p.cmds.size(), dot, sc);
-        if (!p.decl.empty()) {
-            if (p.is_assign) {
-                bool found = false;
-                for (size_t k = sc.size(); k-- > 0 && !found;) {
-                    auto it = sc[k].find(p.decl);
-                    if (it != sc[k].end()) { it->second = v; found = true; }
-                }
-                if (!found) throw Error("undefined variable \"" + p.decl + "\"");
-            } else {
-                sc.back()[p.decl] = v;
-            }
+    void set_var(const Pipeline &p, const Value &v) {
+        if (p.is_assign) {
+            for (size_t k = vars.size(); k-- > frame_base;)
+                if (*vars[k].name == p.decl) { vars[k].v = v; return; }
+            throw Error("undefined variable \"" + p.decl + "\"");
         }
+        vars.push_back({&p.decl, v});
+    }
+
+    const Value *eval_pipe(const Pipeline &p, const Value &dot, Value &h0, Value &h1) {
+        const Value *v = eval_pipe_prefix(p, p.cmds.size(), dot, h0, h1);
+        if (!p.decl.empty()) set_var(p, *v);
         return v;
+    }
+
+    Value eval_pipe_value(const Pipeline &p, const Value &dot) {
+        Value h0, h1;
+        const Value *v = eval_pipe(p, dot, h0, h1);
+        if (v == &h0) return std::move(h0);
+        if (v == &h1) return std::move(h1);
+        return *v;
     }
 
     // `{{ <pipeline> | b64enc }}` printed straight into a top-level file: leave it pending.
-    bool try_defer(const Pipeline &p, const Value &dot, Scopes &sc, std::string &out) {
-        if (!opt.defer_b64 || !opt.pending || capture_depth != 0 || !p.decl.empty()) return false;
-        const Command &last = p.cmds.back();
-        if (p.cmds.size() < 2 || last.args.size() != 1 || last.args[0].kind != Operand::Ident ||
-            last.args[0].text != "b64enc")
-            return false;
+    bool try_defer(const Pipeline &p, const Value &dot, std::string &out) {
+        if (!p.defer_candidate || !opt.defer_b64 || !opt.pending || capture_depth != 0) return false;
         if (opt.pending->size() >= TemplateSet::kMaxPending) return false;
-        Value in = eval_pipe_prefix(p, p.cmds.size() - 1, dot, sc);
-        string_arg(in, "b64enc");                // same refusal as the immediate path
-        std::string s = std::move(in.s);         // a config.toml: do not copy it again
-        if (s.empty()) return true;  // b64enc "" == ""
+        Value h0, h1;
+        const Value *in = eval_pipe_prefix(p, p.cmds.size() - 1, dot, h0, h1);
+        string_arg(*in, "b64enc");               // same refusal as the immediate path
+        if (in->s.empty()) return true;          // b64enc "" == ""
         Pending pd;
-        pd.encoded_len = (s.size() + 2) / 3 * 4;
-        pd.input = std::move(s);
+        pd.encoded_len = (in->s.size() + 2) / 3 * 4;
+        // a computed input (an include's text) is ours to take; a value of the tree is copied once
+        if (in == &h0) pd.input = std::move(h0.s);
+        else if (in == &h1) pd.input = std::move(h1.s);
+        else pd.input = in->s;
         // the placeholder (TemplateSet::placeholder) written in place: 4 id bytes, then filler
         const size_t id = opt.pending->size();
         for (int k = 0; k < 4; ++k) out.push_back((char)(0x10 + ((id >> (12 - 4 * k)) & 0xF)));
@@ -1144,63 +1252,78 @@ struct Exec {
         return true;
     }
 
-    void exec_list(const NodeList &nodes, const Value &dot, Scopes &sc, std::string &out) {
+    static void print_value(std::string &out, const Value &v) {
+        if (v.kind == Value::String) out += v.s;
+        else out += go_print(v);
+    }
+
+    void recycle(Value &h) {   // an include's captured text that has been printed: keep its buffer
+        if (h.kind == Value::String && h.s.capacity() >= 256 && capture_pool.size() < 8) capture_pool.push_back(std::move(h.s));
+    }
+
+    void exec_list(const NodeList &nodes, const Value &dot, std::string &out) {
         for (const auto &nd : nodes) {
             switch (nd->kind) {
             case Node::Text: out += nd->text; break;
             case Node::Action: {
-                if (try_defer(*nd->pipe, dot, sc, out)) break;
-                Value v = eval_pipe(*nd->pipe, dot, sc);
-                if (nd->pipe->decl.empty()) out += go_print(v);
+                if (try_defer(*nd->pipe, dot, out)) break;
+                Value h0, h1;
+                const Value *v = eval_pipe(*nd->pipe, dot, h0, h1);
+                if (nd->pipe->decl.empty()) print_value(out, *v);
+                recycle(h0);
+                recycle(h1);
                 break;
             }
             case Node::If: case Node::With: {
-                sc.emplace_back();
-                Value v = eval_pipe(*nd->pipe, dot, sc);
-                if (truth(v)) {
-                    exec_list(nd->body, nd->kind == Node::With ? v : dot, sc, out);
+                const size_t mark = vars.size();
+                Value h0, h1;
+                const Value *v = eval_pipe(*nd->pipe, dot, h0, h1);
+                if (truth(*v)) {
+                    exec_list(nd->body, nd->kind == Node::With ? *v : dot, out);
                 } else if (nd->has_else) {
-                    exec_list(nd->else_body, dot, sc, out);
+                    exec_list(nd->else_body, dot, out);
                 }
-                sc.pop_back();
+                vars.resize(mark);
                 break;
             }
             case Node::Range: {
-                sc.emplace_back();
-                Value v = eval_pipe(*nd->pipe, dot, sc);
-                std::vector<std::pair<Value, Value>> seq;
+                const size_t mark = vars.size();
+                Value h0, h1;
+                const Value *vp = eval_pipe(*nd->pipe, dot, h0, h1);
+                // the sequence must not move while the body runs (the body may assign variables,
+                // which can reallocate `vars`): hold it by value -- a shared_ptr copy, not a deep one
+                const Value v = *vp;
+                const size_t nv = nd->range_vars.size();
+                size_t count = 0;
+                auto body = [&](const Value &key, const Value &elem) {
+                    const size_t inner = vars.size();
+                    if (nv == 1) vars.push_back({&nd->range_vars[0], elem});
+                    else if (nv == 2) {
+                        vars.push_back({&nd->range_vars[0], key});
+                        vars.push_back({&nd->range_vars[1], elem});
+                    }
+                    exec_list(nd->body, elem, out);
+                    vars.resize(inner);
+                    ++count;
+                };
                 if (v.kind == Value::MapK) {
-                    for (const auto &kv : *v.map) seq.push_back({Value::str(kv.first), kv.second});
+                    for (const auto &kv : *v.map) body(nv == 2 ? Value::str(kv.first) : Value(), kv.second);
                 } else if (v.kind == Value::ListK) {
                     int64_t k = 0;
-                    for (const auto &x : *v.list) seq.push_back({Value::integer(k++), x});
+                    for (const auto &x : *v.list) body(Value::integer(k++), x);
                 } else if (v.kind == Value::Int) {
-                    for (int64_t k = 0; k < v.i; ++k) seq.push_back({Value::integer(k), Value::integer(k)});
+                    for (int64_t k = 0; k < v.i; ++k) body(Value::integer(k), Value::integer(k));
                 } else if (!v.is_nilish()) {
                     throw Error("range can't iterate over " + go_print(v));
                 }
-                if (seq.empty() && nd->has_else) exec_list(nd->else_body, dot, sc, out);
-                for (auto &kv : seq) {
-                    sc.emplace_back();
-                    if (nd->range_vars.size() == 1) sc.back()[nd->range_vars[0]] = kv.second;
-                    else if (nd->range_vars.size() == 2) {
-                        sc.back()[nd->range_vars[0]] = kv.first;
-                        sc.back()[nd->range_vars[1]] = kv.second;
-                    }
-                    exec_list(nd->body, kv.second, sc, out);
-                    sc.pop_back();
-                }
-                sc.pop_back();
+                if (count == 0 && nd->has_else) exec_list(nd->else_body, dot, out);
+                vars.resize(mark);
                 break;
             }
             case Node::Template: {
-                Value d = nd->pipe ? eval_pipe(*nd->pipe, dot, sc) : Value::nil();
-                auto it = ts.templates_.find(nd->text);
-                if (it == ts.templates_.end()) throw Error("template \"" + nd->text + "\" not defined");
-                Scopes inner(1);
-                inner[0]["$"] = d;
                 // {{ template }} writes straight into the output, so deferral stays possible
-                exec_list(it->second, d, inner, out);
+                if (nd->pipe) run_template(nd->text, eval_pipe_value(*nd->pipe, dot), out);
+                else run_template(nd->text, Value::nil(), out);
                 break;
             }
             }
@@ -1221,14 +1344,33 @@ void TemplateSet::parse(const std::string &name, const std::string &src) {
     templates_[name] = nodes;
 }
 
-std::string TemplateSet::execute(const std::string &name, const Value &data, const ExecOptions &opt) const {
+const NodeList *TemplateSet::find(const std::string &name) const {
     auto it = templates_.find(name);
-    if (it == templates_.end()) throw Error("template \"" + name + "\" not defined");
-    Exec ex{*this, opt};
-    Exec::Scopes sc(1);
-    sc[0]["$"] = data;
+    return it == templates_.end() ? nullptr : &it->second;
+}
+
+void TemplateSet::execute_into(const NodeList &nodes, const Value &data, const ExecOptions &opt, std::string &out) const {
+    // the variable stack and the include buffers are kept per thread: a fleet render executes the
+    // same few templates thousands of times on every host thread
+    struct Scratch { std::deque<Var> vars; std::vector<std::string> pool; bool busy = false; };
+    static thread_local Scratch tls;
+    Scratch local;
+    Scratch &sc = tls.busy ? local : tls;   // busy: a nested render from inside a callback
+    struct Guard {
+        Scratch &s;
+        explicit Guard(Scratch &x) : s(x) { s.busy = true; }
+        ~Guard() { s.vars.clear(); s.busy = false; }
+    } guard(sc);
+    Exec ex{*this, opt, 0, sc.vars, sc.pool};
+    sc.vars.push_back({&Exec::dollar(), data});
+    ex.exec_list(nodes, data, out);
+}
+
+std::string TemplateSet::execute(const std::string &name, const Value &data, const ExecOptions &opt) const {
+    const NodeList *nodes = find(name);
+    if (!nodes) throw Error("template \"" + name + "\" not defined");
     std::string out;
-    ex.exec_list(it->second, data, sc, out);
+    execute_into(*nodes, data, opt, out);
     return out;
 }
 
@@ -1245,6 +1387,18 @@ std::string TemplateSet::placeholder(size_t id, size_t encoded_len) {
 bool TemplateSet::has_sentinel_bytes(const std::string &s) {
     const unsigned char *p = reinterpret_cast<const unsigned char *>(s.data());
     size_t n = s.size(), i = 0;
+#ifdef __SSE2__
+    // 64 bytes per step: b == 0x01, or (b & 0xF0) == 0x10
+    const __m128i one = _mm_set1_epi8(0x01), hi = _mm_set1_epi8((char)0xF0), ten = _mm_set1_epi8(0x10);
+    for (; i + 64 <= n; i += 64) {
+        __m128i acc = _mm_setzero_si128();
+        for (int k = 0; k < 4; ++k) {
+            const __m128i v = _mm_loadu_si128(reinterpret_cast<const __m128i *>(p + i + 16 * k));
+            acc = _mm_or_si128(acc, _mm_or_si128(_mm_cmpeq_epi8(v, one), _mm_cmpeq_epi8(_mm_and_si128(v, hi), ten)));
+        }
+        if (_mm_movemask_epi8(acc)) return true;
+    }
+#endif
     const uint64_t ones = 0x0101010101010101ull, highs = 0x8080808080808080ull;
     for (; i + 8 <= n; i += 8) {
         uint64_t w;

@@ -87,6 +87,9 @@ class TemplateSet {
         ImmediateEncoder decode;            // b64dec (optional)
     };
     std::string execute(const std::string &name, const Value &data, const ExecOptions &opt) const;
+    // The same for callers that render one template many times: look it up once, append to `out`.
+    const NodeList *find(const std::string &name) const;
+    void execute_into(const NodeList &nodes, const Value &data, const ExecOptions &opt, std::string &out) const;
 
     // Placeholder protocol (see render.cpp): 4 id bytes in [0x10,0x20) then 0x01 filler.
     static std::string placeholder(size_t id, size_t encoded_len);

@@ -28,8 +28,8 @@ _lib = None
 
 def build(force: bool = False) -> str:
     """Compile ``b64_ref.c`` with gcc (``make -C oracle``)."""
-    src = os.path.join(_HERE, "b64_ref.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("b64_ref.c", "b64_pool.c", "Makefile")]
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(s) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle_b64.so"],
                               stdout=subprocess.DEVNULL)
     return _SO
@@ -55,8 +55,43 @@ def lib() -> ctypes.CDLL:
         L.oracle_b64_decode_batch.restype = None
         L.oracle_b64_decode_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_int64, c.c_void_p,
                                               c.c_void_p, c.c_void_p, c.c_void_p]
+        L.oracle_pool_create.restype = c.c_void_p
+        L.oracle_pool_create.argtypes = [c.c_int]
+        L.oracle_pool_encode_batch.restype = None
+        L.oracle_pool_encode_batch.argtypes = [c.c_void_p, c.c_void_p, c.c_void_p, c.c_int64,
+                                               c.c_void_p, c.c_void_p]
+        L.oracle_pool_destroy.restype = None
+        L.oracle_pool_destroy.argtypes = [c.c_void_p]
         _lib = L
     return _lib
+
+
+class EncodePool:
+    """Persistent C thread pool over the checker's encoder (b64_pool.c): what bench.py's CPU legs
+    time.  Threads are created once; a step only wakes them; the batch is cut by input bytes."""
+
+    def __init__(self, threads: int):
+        self.threads = max(1, int(threads))
+        self._h = lib().oracle_pool_create(self.threads)
+        if not self._h:
+            raise MemoryError("oracle_pool_create")
+
+    def encode_batch(self, blob: np.ndarray, in_off: np.ndarray, out_off: np.ndarray, out: np.ndarray) -> None:
+        assert blob.dtype == np.uint8 and in_off.dtype == np.int64 and out_off.dtype == np.int64
+        assert blob.flags.c_contiguous and in_off.flags.c_contiguous and out_off.flags.c_contiguous
+        lib().oracle_pool_encode_batch(self._h, blob.ctypes.data, in_off.ctypes.data, len(in_off) - 1,
+                                       out.ctypes.data, out_off.ctypes.data)
+
+    def close(self) -> None:
+        if self._h:
+            lib().oracle_pool_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
 
 
 def encoded_len(n: int) -> int:

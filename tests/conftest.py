@@ -11,34 +11,10 @@ REFERENCE = "/root/reference"
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
-def _materialise_reference_chart() -> str:
-    """The reference's chart (deployment/helm, eleven files) rebuilt in a temporary directory
-    from tests/golden/reference_chart_files.json, so that the same tests run in the build
-    container and on the GPU box, where /root/reference does not exist."""
-    import atexit
-    import base64
-    import hashlib
-    import json
-    import shutil
-    import tempfile
-    with open(os.path.join(GOLDEN, "reference_chart_files.json")) as f:
-        frozen = json.load(f)["files"]
-    top = tempfile.mkdtemp(prefix="kvedge_refchart_")
-    atexit.register(shutil.rmtree, top, ignore_errors=True)
-    # the chart directory keeps the reference's own base name: it is not part of any output
-    # (Helm uses Chart.yaml's name), but error messages quote it
-    root = os.path.join(top, "helm")
-    for ent in frozen:
-        raw = base64.b64decode(ent["b64"])
-        assert hashlib.sha256(raw).hexdigest() == ent["sha256"] and len(raw) == ent["len"], ent["path"]
-        dst = os.path.join(root, ent["path"])
-        os.makedirs(os.path.dirname(dst), exist_ok=True)
-        with open(dst, "wb") as out:
-            out.write(raw)
-    return root
+sys.path.insert(0, GOLDEN)
+import refchart  # noqa: E402  tests/golden/refchart.py
 
-
-REF_CHART = _materialise_reference_chart()
+REF_CHART = refchart.materialise()
 REF_CHART_LIVE = os.path.join(REFERENCE, "deployment", "helm")
 
 
