@@ -50,12 +50,17 @@ struct kv_chart {
 };
 
 struct kv_release {
-    std::string manifest;           // helm-template framed stream (placeholders while pending)
-    std::string notes;
+    // The `helm template` stream and the NOTES text as planned: every pending b64enc site is a
+    // 5-byte placeholder (TemplateSet::kPlaceholderLen), so planning never writes or moves the
+    // kilobytes the encodings will take.  The final text is assembled once, when asked for.
+    std::string manifest, notes;
+    size_t manifest_full_size = 0;      // size of the stream once every placeholder is expanded
     std::vector<Pending> pending;
-    std::vector<std::string> filled;  // encoded text per pending site ("" until filled)
+    std::vector<std::string> filled;    // encoded text per pending site ("" until filled)
     size_t n_filled = 0;
-    bool spliced = false;
+    std::string full_manifest, full_notes;
+    bool expanded = false;
+    Value keepalive;                    // the render's value tree: pending inputs may point into it
 };
 
 namespace {
@@ -177,7 +182,7 @@ void prepare_chart(kv_chart *c) {
 
 // Render every non-partial file of the chart, in name order; rendered[k] belongs to c->files[k].
 void render_files(const kv_chart *c, const Value &vals, const char *release, const char *ns, bool defer,
-                  std::vector<Pending> *pending, std::vector<std::string> *rendered) {
+                  std::vector<Pending> *pending, std::vector<std::string> *rendered, Value *keepalive) {
     Value rel = Value::make_map();
     (*rel.map)["Name"] = Value::str(release ? release : "release-name");
     (*rel.map)["Namespace"] = Value::str(ns ? ns : "default");
@@ -195,14 +200,16 @@ void render_files(const kv_chart *c, const Value &vals, const char *release, con
     TemplateSet::ExecOptions opt;
     opt.defer_b64 = defer;
     opt.pending = pending;
+    opt.values_outlive_pending = keepalive != nullptr;
+    if (keepalive) *keepalive = top;
     opt.encode = gpu_encode_one;
     opt.decode = gpu_decode_one;
-    rendered->assign(c->files.size(), std::string());
+    rendered->resize(c->files.size());   // the caller's buffers: their capacity is reused
     for (size_t k = 0; k < c->files.size(); ++k) {
         const kv_chart::File &f = c->files[k];
         tmpl_slot = f.tmpl;
         std::string &out = (*rendered)[k];
-        out.reserve(4096);
+        out.clear();
         try {
             c->ts.execute_into(*f.nodes, top, opt, out);
         } catch (const kvedge::tmpl::Error &e) {
@@ -220,39 +227,51 @@ void frame(const kv_chart *c, const std::vector<std::string> &rendered, std::str
     kvedge::chart::frame_manifests(files, manifest, notes);
 }
 
-// Write every filled encoding over its placeholder (found by its 4 id bytes).
-void splice(std::string &text, const std::vector<Pending> &pending, const std::vector<std::string> &filled) {
-    for (size_t i = 0; i + 4 <= text.size();) {
-        unsigned char c = (unsigned char)text[i];
-        if (c >= 0x10 && c < 0x20) {
+// Walk a planned text: fn_text(ptr, n) for every run of ordinary bytes, fn_site(id) for every
+// placeholder (4 id bytes in 0x10-0x1F, then 0x01).
+template <typename FT, typename FS>
+void walk_planned(const char *text, size_t n, size_t n_pending, FT fn_text, FS fn_site) {
+    constexpr size_t kP = TemplateSet::kPlaceholderLen;
+    size_t run = 0, i = 0;
+    while (i < n) {
+        const unsigned char c = (unsigned char)text[i];
+        if (c >= 0x10 && c < 0x20 && i + kP <= n && text[i + 4] == '\x01') {
             size_t id = 0;
-            for (int k = 0; k < 4; ++k) id = (id << 4) | ((unsigned char)text[i + (size_t)k] & 0xF);
-            if (id < pending.size() && filled[id].size() == pending[id].encoded_len && i + pending[id].encoded_len <= text.size()) {
-                memcpy(&text[i], filled[id].data(), filled[id].size());
-                i += filled[id].size();
+            bool ok = true;
+            for (int k = 0; k < 4; ++k) {
+                const unsigned char b = (unsigned char)text[i + (size_t)k];
+                ok = ok && b >= 0x10 && b < 0x20;
+                id = (id << 4) | (b & 0xF);
+            }
+            if (ok && id < n_pending) {
+                if (i > run) fn_text(text + run, i - run);
+                fn_site(id);
+                i += kP;
+                run = i;
                 continue;
             }
         }
         ++i;
     }
+    if (n > run) fn_text(text + run, n - run);
 }
 
-// The same over a raw buffer, the encodings coming from one packed blob: site k's text is
-// enc[enc_off[k] .. + encoded_len).
-void splice_raw(char *text, size_t n, const std::vector<Pending> &pending, const char *enc, const int64_t *enc_off) {
-    for (size_t i = 0; i + 4 <= n;) {
-        unsigned char c = (unsigned char)text[i];
-        if (c >= 0x10 && c < 0x20) {
-            size_t id = 0;
-            for (int k = 0; k < 4; ++k) id = (id << 4) | ((unsigned char)text[i + (size_t)k] & 0xF);
-            if (id < pending.size() && i + pending[id].encoded_len <= n) {
-                memcpy(text + i, enc + enc_off[id], pending[id].encoded_len);
-                i += pending[id].encoded_len;
-                continue;
-            }
-        }
-        ++i;
-    }
+size_t expanded_size(const std::string &text, const std::vector<Pending> &pending) {
+    size_t total = 0;
+    walk_planned(text.data(), text.size(), pending.size(), [&](const char *, size_t n) { total += n; },
+                 [&](size_t id) { total += pending[id].encoded_len; });
+    return total;
+}
+
+// The final text: ordinary bytes copied, every placeholder replaced by its encoding, which
+// enc_of(id) points at.  Returns the number of bytes written to dst.
+template <typename F>
+size_t expand_into(char *dst, const std::string &text, const std::vector<Pending> &pending, F enc_of) {
+    char *q = dst;
+    walk_planned(text.data(), text.size(), pending.size(),
+                 [&](const char *p, size_t n) { memcpy(q, p, n); q += n; },
+                 [&](size_t id) { memcpy(q, enc_of(id), pending[id].encoded_len); q += pending[id].encoded_len; });
+    return (size_t)(q - dst);
 }
 
 // Run fn(i) for i in [0, n) on all host threads.
@@ -276,15 +295,66 @@ void parallel_for(int n, F fn) {
     for (auto &t : pool) t.join();
 }
 
+// The buffer kv_fleet_template hands out.  A fleet's stream is tens of megabytes: fresh from
+// malloc it arrives as untouched pages and the first write to each of them is a page fault (more
+// time than the encode).  So the last buffer given back through kv_free is kept (one per process)
+// and handed out again when it is big enough; kv_shutdown-less by design: it is ordinary memory.
+std::mutex g_out_mu;
+char *g_out_cached = nullptr;      // owned by the library while g_out_lent is false
+size_t g_out_cap = 0;
+bool g_out_lent = false;
+
+char *out_buffer_get(size_t bytes) {
+    {
+        std::lock_guard<std::mutex> lk(g_out_mu);
+        if (g_out_cached && !g_out_lent && g_out_cap >= bytes) {
+            g_out_lent = true;
+            return g_out_cached;
+        }
+        if (g_out_cached && !g_out_lent) {   // too small: replace it
+            free(g_out_cached);
+            g_out_cached = nullptr;
+            g_out_cap = 0;
+        }
+    }
+    const size_t cap = bytes + bytes / 8 + 4096;
+    char *p = static_cast<char *>(malloc(cap));
+    if (!p) return nullptr;
+    std::lock_guard<std::mutex> lk(g_out_mu);
+    if (!g_out_cached) {      // this one becomes the recycled buffer when it comes back
+        g_out_cached = p;
+        g_out_cap = cap;
+        g_out_lent = true;
+    }
+    return p;
+}
+
+// true: p was the recycled buffer and is now parked instead of freed
+bool out_buffer_put(void *p) {
+    std::lock_guard<std::mutex> lk(g_out_mu);
+    if (p && p == g_out_cached && g_out_lent) {
+        if (g_out_cap > ((size_t)1 << 30)) {   // do not sit on more than 1 GiB
+            g_out_cached = nullptr;
+            g_out_cap = 0;
+            g_out_lent = false;
+            return false;
+        }
+        g_out_lent = false;
+        return true;
+    }
+    return false;
+}
+
 int plan_release(const kv_chart *c, const char *release, const char *ns, const kv_overrides *ov, bool defer,
                  kv_release **out) {
     std::unique_ptr<kv_release> r(new kv_release);
     bool user_sentinels = false;
     Value vals = merged_values(c, ov, &user_sentinels);
     const bool can_defer = defer && !c->templates_have_sentinels && !c->defaults_have_sentinels && !user_sentinels;
-    std::vector<std::string> rendered;
-    render_files(c, vals, release, ns, can_defer, &r->pending, &rendered);
+    static thread_local std::vector<std::string> rendered;   // per-file output, capacity kept per thread
+    render_files(c, vals, release, ns, can_defer, &r->pending, &rendered, &r->keepalive);
     frame(c, rendered, &r->manifest, &r->notes);
+    r->manifest_full_size = expanded_size(r->manifest, r->pending);
     r->filled.assign(r->pending.size(), std::string());
     *out = r.release();
     return KV_OK;
@@ -328,8 +398,8 @@ int kv_release_pending_count(const kv_release *r) { return r ? (int)r->pending.s
 
 int kv_release_pending_input(const kv_release *r, int i, const uint8_t **data, size_t *len) {
     if (!r || i < 0 || (size_t)i >= r->pending.size() || !data || !len) return fail(KV_EINVAL, "bad pending index");
-    *data = reinterpret_cast<const uint8_t *>(r->pending[(size_t)i].input.data());
-    *len = r->pending[(size_t)i].input.size();
+    *data = reinterpret_cast<const uint8_t *>(r->pending[(size_t)i].data());
+    *len = r->pending[(size_t)i].size();
     return KV_OK;
 }
 
@@ -340,7 +410,7 @@ int kv_release_pending_fill(kv_release *r, int i, const char *enc, size_t len) {
                                    std::to_string(r->pending[(size_t)i].encoded_len));
     if (r->filled[(size_t)i].empty()) ++r->n_filled;
     r->filled[(size_t)i].assign(enc, len);
-    r->spliced = false;
+    r->expanded = false;
     return KV_OK;
 }
 
@@ -350,19 +420,19 @@ int kv_release_encode_gpu(kv_release *r) {
     if (n == 0) return KV_OK;
     std::vector<int64_t> in_off(n + 1, 0), out_off(n + 1, 0);
     for (size_t i = 0; i < n; ++i) {
-        in_off[i + 1] = in_off[i] + (int64_t)r->pending[i].input.size();
+        in_off[i + 1] = in_off[i] + (int64_t)r->pending[i].size();
         out_off[i + 1] = out_off[i] + (int64_t)((r->pending[i].encoded_len + 15) / 16 * 16);
     }
     std::string blob;
     blob.reserve((size_t)in_off[n]);
-    for (size_t i = 0; i < n; ++i) blob += r->pending[i].input;
+    for (size_t i = 0; i < n; ++i) blob.append(r->pending[i].data(), r->pending[i].size());
     std::string enc((size_t)out_off[n], '\0');
     int rc = kv_b64enc_batch(reinterpret_cast<const uint8_t *>(blob.data()), in_off.data(), (int64_t)n, &enc[0],
                              out_off.data());
     if (rc != KV_OK) return rc;
     for (size_t i = 0; i < n; ++i) r->filled[i].assign(enc, (size_t)out_off[i], r->pending[i].encoded_len);
     r->n_filled = n;
-    r->spliced = false;
+    r->expanded = false;
     return KV_OK;
 }
 
@@ -370,10 +440,13 @@ static int finish(kv_release *r) {
     if (r->n_filled < r->pending.size())
         return fail(KV_EINVAL, std::to_string(r->pending.size() - r->n_filled) +
                                    " b64enc site(s) still pending: call kv_release_encode_gpu first");
-    if (!r->spliced) {
-        splice(r->manifest, r->pending, r->filled);
-        splice(r->notes, r->pending, r->filled);
-        r->spliced = true;
+    if (!r->expanded) {
+        auto enc_of = [&](size_t id) { return r->filled[id].data(); };
+        r->full_manifest.resize(r->manifest_full_size);
+        expand_into(&r->full_manifest[0], r->manifest, r->pending, enc_of);
+        r->full_notes.resize(expanded_size(r->notes, r->pending));
+        expand_into(&r->full_notes[0], r->notes, r->pending, enc_of);
+        r->expanded = true;
     }
     return KV_OK;
 }
@@ -382,8 +455,8 @@ int kv_release_manifest(kv_release *r, const char **data, size_t *len) {
     if (!r || !data || !len) return fail(KV_EINVAL, "null argument");
     int rc = finish(r);
     if (rc) return rc;
-    *data = r->manifest.data();
-    *len = r->manifest.size();
+    *data = r->full_manifest.data();
+    *len = r->full_manifest.size();
     return KV_OK;
 }
 
@@ -391,8 +464,8 @@ int kv_release_notes(kv_release *r, const char **data, size_t *len) {
     if (!r || !data || !len) return fail(KV_EINVAL, "null argument");
     int rc = finish(r);
     if (rc) return rc;
-    *data = r->notes.data();
-    *len = r->notes.size();
+    *data = r->full_notes.data();
+    *len = r->full_notes.size();
     return KV_OK;
 }
 
@@ -480,12 +553,13 @@ int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *
         if (first_rc.load() != KV_OK) return fail(first_rc.load(), err_msg);
     }
     lap("plan (all host threads)");
-    // One packed batch over every pending Secret payload of the fleet.  A placeholder is exactly
-    // as long as its encoding, so every manifest already has its final size: the output buffer is
-    // laid out before anything is encoded, and all copying is done by all host threads.
+    // One packed batch over every pending Secret payload of the fleet.  The planned manifests
+    // hold 5-byte placeholders and know their final size, so the output buffer is laid out before
+    // anything is encoded; afterwards every output byte is written exactly once, by all host
+    // threads: ordinary text from the planned manifest, encodings straight from the staging blob.
     std::vector<size_t> man_off((size_t)n_releases + 1, 0), unit_base((size_t)n_releases + 1, 0);
     for (int i = 0; i < n_releases; ++i) {
-        man_off[(size_t)i + 1] = man_off[(size_t)i] + rel[(size_t)i]->manifest.size();
+        man_off[(size_t)i + 1] = man_off[(size_t)i] + rel[(size_t)i]->manifest_full_size;
         unit_base[(size_t)i + 1] = unit_base[(size_t)i] + rel[(size_t)i]->pending.size();
     }
     const int64_t n_units = (int64_t)unit_base[(size_t)n_releases];
@@ -494,7 +568,7 @@ int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *
         size_t u = 0;
         for (auto &r : rel)
             for (auto &p : r->pending) {
-                in_off[u + 1] = in_off[u] + (int64_t)p.input.size();
+                in_off[u + 1] = in_off[u] + (int64_t)p.size();
                 enc_off[u + 1] = enc_off[u] + (int64_t)((p.encoded_len + 15) / 16 * 16);
                 ++u;
             }
@@ -505,32 +579,32 @@ int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *
     char *stage_in = nullptr, *stage_out = nullptr;
     int rc = kv_stage_get_((size_t)in_off[(size_t)n_units], (size_t)enc_off[(size_t)n_units], &stage_in, &stage_out);
     if (rc) return rc;
-    char *buf = static_cast<char *>(malloc(total_out + 1));
+    char *buf = out_buffer_get(total_out + 1);
     if (!buf) return fail(KV_ENOMEM, "malloc");
     parallel_for(n_releases, [&](int i) {
         kv_release &r = *rel[(size_t)i];
         size_t u = unit_base[(size_t)i];
-        for (auto &p : r.pending) memcpy(stage_in + in_off[u++], p.input.data(), p.input.size());
-        memcpy(buf + man_off[(size_t)i], r.manifest.data(), r.manifest.size());
+        for (auto &p : r.pending) memcpy(stage_in + in_off[u++], p.data(), p.size());
     });
-    lap("pack inputs, lay out manifests");
+    lap("pack inputs");
     if (n_units > 0) {
         rc = kv_b64enc_batch(reinterpret_cast<const uint8_t *>(stage_in), in_off.data(), n_units, stage_out, enc_off.data());
         if (rc) {
-            free(buf);
+            kv_free(buf);
             return rc;
         }
     }
     lap("kv_b64enc_batch");
     parallel_for(n_releases, [&](int i) {
         kv_release &r = *rel[(size_t)i];
-        splice_raw(buf + man_off[(size_t)i], r.manifest.size(), r.pending, stage_out, &enc_off[unit_base[(size_t)i]]);
+        const int64_t *eo = &enc_off[unit_base[(size_t)i]];
+        expand_into(buf + man_off[(size_t)i], r.manifest, r.pending, [&](size_t id) { return stage_out + eo[id]; });
         rel[(size_t)i].reset();   // freed here, on this thread, not one by one when the function returns
     });
     for (int i = 0; i <= n_releases; ++i) out_off[i] = (int64_t)man_off[(size_t)i];
     buf[total_out] = 0;
     *out = buf;
-    lap("splice");
+    lap("assemble");
     return KV_OK;
 }
 
@@ -602,7 +676,8 @@ int kv_helm_lint(const char *chart_dir, const kv_overrides *overrides, int *ok, 
             std::vector<Pending> pending;
             const bool defer = !c->templates_have_sentinels && !c->defaults_have_sentinels && !user_sentinels;
             std::vector<std::string> rendered;
-            render_files(c, vals, "test-release", "default", defer, &pending, &rendered);
+            Value keep;
+            render_files(c, vals, "test-release", "default", defer, &pending, &rendered, &keep);
             std::map<std::string, std::string> files;
             for (size_t k = 0; k < rendered.size(); ++k) files[c->files[k].name] = rendered[k];
             std::vector<Manifest> ms;
@@ -653,6 +728,8 @@ int kv_helm_lint(const char *chart_dir, const kv_overrides *overrides, int *ok, 
     return KV_OK;
 }
 
-void kv_free(void *p) { free(p); }
+void kv_free(void *p) {
+    if (!out_buffer_put(p)) free(p);
+}
 
 }  // extern "C"

@@ -995,7 +995,8 @@ struct Exec {
             if (!capture_pool.empty()) { buf = std::move(capture_pool.back()); capture_pool.pop_back(); buf.clear(); }
             ++capture_depth;
             try {
-                run_template(strval(a[0]), a[1], buf);
+                if (a[0].kind == Value::String) run_template(a[0].s, a[1], buf);
+                else run_template(strval(a[0]), a[1], buf);
             } catch (...) {
                 --capture_depth;
                 throw;
@@ -1239,15 +1240,21 @@ struct Exec {
         string_arg(*in, "b64enc");               // same refusal as the immediate path
         if (in->s.empty()) return true;          // b64enc "" == ""
         Pending pd;
-        pd.encoded_len = (in->s.size() + 2) / 3 * 4;
-        // a computed input (an include's text) is ours to take; a value of the tree is copied once
-        if (in == &h0) pd.input = std::move(h0.s);
-        else if (in == &h1) pd.input = std::move(h1.s);
-        else pd.input = in->s;
-        // the placeholder (TemplateSet::placeholder) written in place: 4 id bytes, then filler
+        pd.len = in->s.size();
+        pd.encoded_len = (pd.len + 2) / 3 * 4;
+        // a computed input (an include's text) is ours to take; a field of a map of the value
+        // tree stays where it is when the caller keeps the tree; anything else is copied
+        const Operand &src = p.cmds[0].args[0];
+        const bool in_tree = opt.values_outlive_pending && p.cmds.size() == 2 && p.cmds[0].args.size() == 1 &&
+                             !src.fields.empty() && (src.kind == Operand::Field || src.kind == Operand::Var);
+        if (in == &h0) pd.owned = std::move(h0.s);
+        else if (in == &h1) pd.owned = std::move(h1.s);
+        else if (in_tree) pd.ext = in->s.data();
+        else pd.owned = in->s;
+        // the placeholder (TemplateSet::placeholder), written in place
         const size_t id = opt.pending->size();
         for (int k = 0; k < 4; ++k) out.push_back((char)(0x10 + ((id >> (12 - 4 * k)) & 0xF)));
-        out.append(pd.encoded_len - 4, '\x01');
+        out.push_back('\x01');
         opt.pending->push_back(std::move(pd));
         return true;
     }
@@ -1354,8 +1361,9 @@ void TemplateSet::execute_into(const NodeList &nodes, const Value &data, const E
     // same few templates thousands of times on every host thread
     struct Scratch { std::deque<Var> vars; std::vector<std::string> pool; bool busy = false; };
     static thread_local Scratch tls;
-    Scratch local;
-    Scratch &sc = tls.busy ? local : tls;   // busy: a nested render from inside a callback
+    std::unique_ptr<Scratch> local;   // only for a nested render from inside a callback
+    if (tls.busy) local.reset(new Scratch);
+    Scratch &sc = local ? *local : tls;
     struct Guard {
         Scratch &s;
         explicit Guard(Scratch &x) : s(x) { s.busy = true; }
@@ -1374,8 +1382,8 @@ std::string TemplateSet::execute(const std::string &name, const Value &data, con
     return out;
 }
 
-std::string TemplateSet::placeholder(size_t id, size_t encoded_len) {
-    std::string s(encoded_len, '\x01');
+std::string TemplateSet::placeholder(size_t id) {
+    std::string s(kPlaceholderLen, '\x01');
     for (int k = 0; k < 4; ++k) s[(size_t)k] = (char)(0x10 + ((id >> (12 - 4 * k)) & 0xF));
     return s;
 }

@@ -60,11 +60,16 @@ std::string format_float(double f);    // Go %v of a float64
 std::string go_quote(const std::string &s);  // strconv.Quote
 Value deep_copy(const Value &v);
 
-// A b64enc site whose evaluation is deferred to the GPU: the input bytes are kept and the
-// output carries a placeholder of exactly the encoded length.
+// A b64enc site whose evaluation is deferred to the GPU: the output carries a short placeholder
+// (kPlaceholderLen bytes) and the input bytes are remembered here -- as a view when they are a
+// value of the tree the caller keeps alive (a config.toml is not copied again), else owned.
 struct Pending {
-    std::string input;
+    std::string owned;
+    const char *ext = nullptr;
+    size_t len = 0;
     size_t encoded_len = 0;
+    const char *data() const { return ext ? ext : owned.data(); }
+    size_t size() const { return len; }
 };
 
 // Called for every `b64enc` the executor cannot defer (its result feeds another function).
@@ -83,6 +88,7 @@ class TemplateSet {
     struct ExecOptions {
         bool defer_b64 = false;             // leave top-level `... | b64enc` sites pending
         std::vector<Pending> *pending = nullptr;
+        bool values_outlive_pending = false;  // the caller keeps `data` alive as long as `pending`
         ImmediateEncoder encode;            // required whenever a b64enc must run now
         ImmediateEncoder decode;            // b64dec (optional)
     };
@@ -91,8 +97,9 @@ class TemplateSet {
     const NodeList *find(const std::string &name) const;
     void execute_into(const NodeList &nodes, const Value &data, const ExecOptions &opt, std::string &out) const;
 
-    // Placeholder protocol (see render.cpp): 4 id bytes in [0x10,0x20) then 0x01 filler.
-    static std::string placeholder(size_t id, size_t encoded_len);
+    // Placeholder protocol (render_capi.cpp expands it): 4 id bytes in [0x10,0x20), then 0x01.
+    static constexpr size_t kPlaceholderLen = 5;
+    static std::string placeholder(size_t id);
     static bool has_sentinel_bytes(const std::string &s);
     static constexpr size_t kMaxPending = 65536;
 

@@ -402,7 +402,7 @@ def test_plan_then_run_equals_batch_equals_oracle(torch_cuda):
     which is what the split exists for."""
     torch = torch_cuda
     rng = np.random.default_rng(21)
-    units = _short_and_long_units(rng, 3000)
+    units = [rng.bytes(s) for s in _short_and_long_units(rng, 3000)]
     blob, in_off = workload.pack(units)
     out_off = b64.encode_offsets(in_off, align=16)
     n = len(units)
