@@ -623,7 +623,7 @@ void coalesce_tables(tmpl::Map &dst, const tmpl::Map &src) {
     for (const auto &kv : src) {
         auto it = dst.find(kv.first);
         if (it == dst.end()) {
-            dst[kv.first] = tmpl::deep_copy(kv.second);
+            dst[kv.first] = kv.second;   // shared, not copied: nothing mutates a value tree after this merge
         } else if (it->second.kind == Value::Nil) {
             dst.erase(it);                                  // "when the YAML value is null, we remove it"
         } else if (kv.second.kind == Value::MapK && it->second.kind == Value::MapK) {
@@ -636,7 +636,10 @@ void coalesce_tables(tmpl::Map &dst, const tmpl::Map &src) {
 
 Value coalesce_values(const Value &defaults, Value user) {
     if (user.kind != Value::MapK) user = Value::make_map();
-    if (defaults.kind == Value::MapK) coalesce_tables(*user.map, *defaults.map);
+    if (defaults.kind == Value::MapK) {
+        user.map->reserve(user.map->size() + defaults.map->size());
+        coalesce_tables(*user.map, *defaults.map);
+    }
     return user;
 }
 

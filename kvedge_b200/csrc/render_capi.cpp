@@ -16,6 +16,7 @@
 #include <memory>
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -139,6 +140,7 @@ Value merged_values(const kv_chart *c, const kv_overrides *ov, bool *user_sentin
     // Helm collects the flags into a map of their own and then slides the chart's defaults
     // under it (chartutil.CoalesceValues): null deletes a default, lists are not patched.
     Value vals = Value::make_map();
+    vals.map->reserve(16);
     for (int i = 0; i < ov->n_set; ++i) kvedge::chart::apply_set(vals, ov->set[i], false);
     for (int i = 0; i < ov->n_set_string; ++i) kvedge::chart::apply_set(vals, ov->set_string[i], true);
     for (int i = 0; i < ov->n_set_file; ++i) kvedge::chart::apply_set_file(vals, ov->set_file[i]);
@@ -184,6 +186,7 @@ void prepare_chart(kv_chart *c) {
 void render_files(const kv_chart *c, const Value &vals, const char *release, const char *ns, bool defer,
                   std::vector<Pending> *pending, std::vector<std::string> *rendered, Value *keepalive) {
     Value rel = Value::make_map();
+    rel.map->reserve(6);
     (*rel.map)["Name"] = Value::str(release ? release : "release-name");
     (*rel.map)["Namespace"] = Value::str(ns ? ns : "default");
     (*rel.map)["IsUpgrade"] = Value::boolean(false);
@@ -191,6 +194,7 @@ void render_files(const kv_chart *c, const Value &vals, const char *release, con
     (*rel.map)["Revision"] = Value::integer(1);
     (*rel.map)["Service"] = Value::str("Helm");
     Value top = Value::make_map();
+    top.map->reserve(5);
     (*top.map)["Values"] = vals;
     (*top.map)["Chart"] = c->chart_meta;
     (*top.map)["Release"] = rel;
@@ -514,93 +518,141 @@ int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *
         fprintf(stderr, "kv_fleet_template: %-28s %8.3f ms\n", what, t - t_prev);
         t_prev = t;
     };
+    // Installs are independent (README.md:72).  One team of host threads carries the whole call
+    // through its phases -- plan, pack, [one GPU batch], assemble -- and thread t keeps the same
+    // installs in every phase, so what a thread allocates while planning it frees itself while
+    // assembling (no cross-thread frees in the allocator) and no phase pays for new threads.
     std::vector<std::unique_ptr<kv_release>> rel((size_t)n_releases);
-    {
-        // Installs are independent: plan them on all host threads (the templates are parsed
-        // once and only read here; every release owns its values and output).
-        unsigned n_thr = std::thread::hardware_concurrency();
-        if (n_thr == 0) n_thr = 1;
-        if (n_thr > 64) n_thr = 64;
-        if ((int)n_thr > n_releases) n_thr = (unsigned)(n_releases > 0 ? n_releases : 1);
-        std::atomic<int> next{0};
-        std::atomic<int> first_rc{KV_OK};
-        std::mutex err_mu;
-        std::string err_msg;
-        auto work = [&]() {
-            for (;;) {
-                const int i = next.fetch_add(1);
-                if (i >= n_releases || first_rc.load() != KV_OK) return;
-                try {
-                    kv_release *r = nullptr;
-                    int rc = plan_release(chart, release_names ? release_names[i] : nullptr, ns,
-                                          overrides ? &overrides[i] : nullptr, true, &r);
-                    if (rc) throw kvedge::tmpl::Error(kv_last_error());
-                    rel[(size_t)i].reset(r);
-                } catch (const std::exception &e) {
-                    std::lock_guard<std::mutex> lk(err_mu);
-                    if (first_rc.load() == KV_OK) {
-                        err_msg = e.what();
-                        first_rc.store(KV_ETEMPLATE);
-                    }
-                    return;
-                }
+    unsigned n_thr = std::thread::hardware_concurrency();
+    if (n_thr == 0) n_thr = 1;
+    if (n_thr > 64) n_thr = 64;
+    constexpr int kBlock = 8;   // installs per turn of a thread
+    const int n_blocks = (n_releases + kBlock - 1) / kBlock;
+    if ((int)n_thr > n_blocks) n_thr = (unsigned)(n_blocks > 0 ? n_blocks : 1);
+
+    struct Barrier {
+        std::mutex mu;
+        std::condition_variable cv;
+        unsigned waiting = 0, team;
+        unsigned long generation = 0;
+        explicit Barrier(unsigned n) : team(n) {}
+        void wait() {
+            std::unique_lock<std::mutex> lk(mu);
+            const unsigned long gen = generation;
+            if (++waiting == team) {
+                waiting = 0;
+                ++generation;
+                cv.notify_all();
+            } else {
+                cv.wait(lk, [&] { return generation != gen; });
             }
-        };
-        std::vector<std::thread> pool;
-        for (unsigned t = 1; t < n_thr; ++t) pool.emplace_back(work);
-        work();
-        for (auto &t : pool) t.join();
-        if (first_rc.load() != KV_OK) return fail(first_rc.load(), err_msg);
-    }
-    lap("plan (all host threads)");
-    // One packed batch over every pending Secret payload of the fleet.  The planned manifests
-    // hold 5-byte placeholders and know their final size, so the output buffer is laid out before
-    // anything is encoded; afterwards every output byte is written exactly once, by all host
-    // threads: ordinary text from the planned manifest, encodings straight from the staging blob.
-    std::vector<size_t> man_off((size_t)n_releases + 1, 0), unit_base((size_t)n_releases + 1, 0);
-    for (int i = 0; i < n_releases; ++i) {
-        man_off[(size_t)i + 1] = man_off[(size_t)i] + rel[(size_t)i]->manifest_full_size;
-        unit_base[(size_t)i + 1] = unit_base[(size_t)i] + rel[(size_t)i]->pending.size();
-    }
-    const int64_t n_units = (int64_t)unit_base[(size_t)n_releases];
-    std::vector<int64_t> in_off((size_t)n_units + 1, 0), enc_off((size_t)n_units + 1, 0);
-    {
-        size_t u = 0;
-        for (auto &r : rel)
-            for (auto &p : r->pending) {
-                in_off[u + 1] = in_off[u] + (int64_t)p.size();
-                enc_off[u + 1] = enc_off[u] + (int64_t)((p.encoded_len + 15) / 16 * 16);
-                ++u;
-            }
-    }
-    const size_t total_out = man_off[(size_t)n_releases];
-    static std::mutex stage_mu;   // the staging buffers are one per process
-    std::lock_guard<std::mutex> stage_lock(stage_mu);
-    char *stage_in = nullptr, *stage_out = nullptr;
-    int rc = kv_stage_get_((size_t)in_off[(size_t)n_units], (size_t)enc_off[(size_t)n_units], &stage_in, &stage_out);
-    if (rc) return rc;
-    char *buf = out_buffer_get(total_out + 1);
-    if (!buf) return fail(KV_ENOMEM, "malloc");
-    parallel_for(n_releases, [&](int i) {
-        kv_release &r = *rel[(size_t)i];
-        size_t u = unit_base[(size_t)i];
-        for (auto &p : r.pending) memcpy(stage_in + in_off[u++], p.data(), p.size());
-    });
-    lap("pack inputs");
-    if (n_units > 0) {
-        rc = kv_b64enc_batch(reinterpret_cast<const uint8_t *>(stage_in), in_off.data(), n_units, stage_out, enc_off.data());
-        if (rc) {
-            kv_free(buf);
-            return rc;
         }
+    } barrier(n_thr);
+
+    std::atomic<int> first_rc{KV_OK};
+    std::mutex err_mu;
+    std::string err_msg;
+    auto set_error = [&](int code, const std::string &msg) {
+        std::lock_guard<std::mutex> lk(err_mu);
+        if (first_rc.load() == KV_OK) {
+            err_msg = msg;
+            first_rc.store(code);
+        }
+    };
+    // shared between the phases; written by thread 0 between barriers
+    std::vector<size_t> man_off((size_t)n_releases + 1, 0), unit_base((size_t)n_releases + 1, 0);
+    std::vector<int64_t> in_off, enc_off;
+    char *stage_in = nullptr, *stage_out = nullptr, *buf = nullptr;
+    size_t total_out = 0;
+    static std::mutex stage_mu;   // the staging buffers are one per process
+    std::unique_lock<std::mutex> stage_lock(stage_mu, std::defer_lock);
+
+    auto for_my_installs = [&](unsigned t, auto fn) {
+        for (int b = (int)t; b < n_blocks; b += (int)n_thr)
+            for (int i = b * kBlock; i < n_releases && i < (b + 1) * kBlock; ++i) fn(i);
+    };
+    auto team_member = [&](unsigned t) {
+        // ---- plan
+        for_my_installs(t, [&](int i) {
+            if (first_rc.load() != KV_OK) return;
+            try {
+                kv_release *r = nullptr;
+                int rc = plan_release(chart, release_names ? release_names[i] : nullptr, ns,
+                                      overrides ? &overrides[i] : nullptr, true, &r);
+                if (rc) throw kvedge::tmpl::Error(kv_last_error());
+                rel[(size_t)i].reset(r);
+            } catch (const std::exception &e) {
+                set_error(KV_ETEMPLATE, e.what());
+            }
+        });
+        barrier.wait();
+        if (t == 0 && first_rc.load() == KV_OK) {
+            lap("plan (all host threads)");
+            // One packed batch over every pending Secret payload of the fleet.  The planned
+            // manifests hold 5-byte placeholders and know their final size, so the output is laid
+            // out before anything is encoded; afterwards every output byte is written exactly
+            // once: ordinary text from the planned manifest, encodings from the staging blob.
+            for (int i = 0; i < n_releases; ++i) {
+                man_off[(size_t)i + 1] = man_off[(size_t)i] + rel[(size_t)i]->manifest_full_size;
+                unit_base[(size_t)i + 1] = unit_base[(size_t)i] + rel[(size_t)i]->pending.size();
+            }
+            const size_t n_units = unit_base[(size_t)n_releases];
+            in_off.assign(n_units + 1, 0);
+            enc_off.assign(n_units + 1, 0);
+            size_t u = 0;
+            for (auto &r : rel)
+                for (auto &p : r->pending) {
+                    in_off[u + 1] = in_off[u] + (int64_t)p.size();
+                    enc_off[u + 1] = enc_off[u] + (int64_t)((p.encoded_len + 15) / 16 * 16);
+                    ++u;
+                }
+            total_out = man_off[(size_t)n_releases];
+            stage_lock.lock();
+            int rc = kv_stage_get_((size_t)in_off[n_units], (size_t)enc_off[n_units], &stage_in, &stage_out);
+            if (rc) set_error(rc, kv_last_error());
+            else if (!(buf = out_buffer_get(total_out + 1))) set_error(KV_ENOMEM, "malloc");
+        }
+        barrier.wait();
+        // ---- pack
+        if (first_rc.load() == KV_OK)
+            for_my_installs(t, [&](int i) {
+                size_t u = unit_base[(size_t)i];
+                for (auto &p : rel[(size_t)i]->pending) memcpy(stage_in + in_off[u++], p.data(), p.size());
+            });
+        barrier.wait();
+        if (t == 0 && first_rc.load() == KV_OK) {
+            lap("pack inputs");
+            const int64_t n_units = (int64_t)unit_base[(size_t)n_releases];
+            if (n_units > 0) {
+                int rc = kv_b64enc_batch(reinterpret_cast<const uint8_t *>(stage_in), in_off.data(), n_units, stage_out,
+                                         enc_off.data());
+                if (rc) set_error(rc, kv_last_error());
+            }
+            lap("kv_b64enc_batch");
+        }
+        barrier.wait();
+        // ---- assemble, and free what this thread planned
+        const bool ok = first_rc.load() == KV_OK;
+        for_my_installs(t, [&](int i) {
+            if (!rel[(size_t)i]) return;
+            if (ok) {
+                kv_release &r = *rel[(size_t)i];
+                const int64_t *eo = &enc_off[unit_base[(size_t)i]];
+                expand_into(buf + man_off[(size_t)i], r.manifest, r.pending, [&](size_t id) { return stage_out + eo[id]; });
+            }
+            rel[(size_t)i].reset();
+        });
+    };
+    {
+        std::vector<std::thread> team;
+        for (unsigned t = 1; t < n_thr; ++t) team.emplace_back(team_member, t);
+        team_member(0);
+        for (auto &th : team) th.join();
     }
-    lap("kv_b64enc_batch");
-    parallel_for(n_releases, [&](int i) {
-        kv_release &r = *rel[(size_t)i];
-        const int64_t *eo = &enc_off[unit_base[(size_t)i]];
-        expand_into(buf + man_off[(size_t)i], r.manifest, r.pending, [&](size_t id) { return stage_out + eo[id]; });
-        rel[(size_t)i].reset();   // freed here, on this thread, not one by one when the function returns
-    });
+    if (first_rc.load() != KV_OK) {
+        if (buf) kv_free(buf);
+        return fail(first_rc.load(), err_msg);
+    }
     for (int i = 0; i <= n_releases; ++i) out_off[i] = (int64_t)man_off[(size_t)i];
     buf[total_out] = 0;
     *out = buf;

@@ -28,7 +28,35 @@ struct Error : std::runtime_error {
 
 struct Value;
 using List = std::vector<Value>;
-using Map = std::map<std::string, Value>;
+
+// map[string]interface{}: a vector kept sorted by key (Go prints and ranges over maps in key
+// order).  Charts' tables hold a handful of entries and a fleet builds several of them per
+// install, so one allocation per table beats one per entry; lookups are a binary search.
+class Map {
+  public:
+    using value_type = std::pair<std::string, Value>;
+    using iterator = std::vector<value_type>::iterator;
+    using const_iterator = std::vector<value_type>::const_iterator;
+    Map();
+    Map(const Map &);
+    Map &operator=(const Map &);
+    ~Map();
+    iterator begin();
+    iterator end();
+    const_iterator begin() const;
+    const_iterator end() const;
+    iterator find(const std::string &k);
+    const_iterator find(const std::string &k) const;
+    Value &operator[](const std::string &k);   // inserts a nil Value when the key is new
+    size_t count(const std::string &k) const;
+    void erase(iterator it);
+    size_t size() const;
+    bool empty() const;
+    void reserve(size_t n);
+
+  private:
+    std::vector<value_type> v_;
+};
 
 struct Value {
     enum Kind { Nil, NoValue, Bool, Int, Float, String, ListK, MapK, StructK };
@@ -53,6 +81,44 @@ struct Value {
     }
     bool is_nilish() const { return kind == Nil || kind == NoValue; }
 };
+
+inline Map::Map() = default;
+inline Map::Map(const Map &) = default;
+inline Map &Map::operator=(const Map &) = default;
+inline Map::~Map() = default;
+inline Map::iterator Map::begin() { return v_.begin(); }
+inline Map::iterator Map::end() { return v_.end(); }
+inline Map::const_iterator Map::begin() const { return v_.begin(); }
+inline Map::const_iterator Map::end() const { return v_.end(); }
+inline Map::const_iterator Map::find(const std::string &k) const {
+    size_t lo = 0, hi = v_.size();
+    while (lo < hi) {
+        const size_t mid = (lo + hi) / 2;
+        const int c = v_[mid].first.compare(k);
+        if (c == 0) return v_.begin() + (std::ptrdiff_t)mid;
+        if (c < 0) lo = mid + 1; else hi = mid;
+    }
+    return v_.end();
+}
+inline Map::iterator Map::find(const std::string &k) {
+    const const_iterator it = static_cast<const Map *>(this)->find(k);
+    return v_.begin() + (it - v_.cbegin());
+}
+inline Value &Map::operator[](const std::string &k) {
+    size_t lo = 0, hi = v_.size();
+    while (lo < hi) {
+        const size_t mid = (lo + hi) / 2;
+        const int c = v_[mid].first.compare(k);
+        if (c == 0) return v_[mid].second;
+        if (c < 0) lo = mid + 1; else hi = mid;
+    }
+    return v_.insert(v_.begin() + (std::ptrdiff_t)lo, value_type(k, Value()))->second;
+}
+inline size_t Map::count(const std::string &k) const { return find(k) == end() ? 0 : 1; }
+inline void Map::erase(iterator it) { v_.erase(it); }
+inline size_t Map::size() const { return v_.size(); }
+inline bool Map::empty() const { return v_.empty(); }
+inline void Map::reserve(size_t n) { v_.reserve(n); }
 
 bool truth(const Value &v);            // text/template truth
 std::string go_print(const Value &v);  // fmt.Fprint of one value
