@@ -28,7 +28,7 @@ _lib = None
 
 def build(force: bool = False) -> str:
     """Compile ``b64_ref.c`` with gcc (``make -C oracle``)."""
-    srcs = [os.path.join(_HERE, f) for f in ("b64_ref.c", "b64_pool.c", "Makefile")]
+    srcs = [os.path.join(_HERE, f) for f in ("b64_ref.c", "b64_pool.c", "fleet_cpu.c", "Makefile")]
     if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(s) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle_b64.so"],
                               stdout=subprocess.DEVNULL)
@@ -62,6 +62,11 @@ def lib() -> ctypes.CDLL:
                                                c.c_void_p, c.c_void_p]
         L.oracle_pool_destroy.restype = None
         L.oracle_pool_destroy.argtypes = [c.c_void_p]
+        L.oracle_fleet_render_cpu.restype = c.c_int
+        L.oracle_fleet_render_cpu.argtypes = [c.c_void_p, c.c_void_p, c.c_int, c.c_void_p, c.c_char_p, c.c_void_p,
+                                              c.c_int, c.POINTER(c.c_void_p), c.c_void_p]
+        L.oracle_free.restype = None
+        L.oracle_free.argtypes = [c.c_void_p]
         _lib = L
     return _lib
 
@@ -185,3 +190,21 @@ def decode_batch(blob: np.ndarray, in_off: np.ndarray, out_off: np.ndarray):
     lib().oracle_b64_decode_batch(blob.ctypes.data, in_off.ctypes.data, n, out.ctypes.data,
                                   out_off.ctypes.data, out_len.ctypes.data, status.ctypes.data)
     return out[:cap], out_len[:n], status[:n]
+
+
+def fleet_render_cpu(product_lib, chart_handle, n: int, names_arr, namespace: bytes, overrides_arr, threads: int):
+    """bench.py's CPU twin of kv_fleet_template (fleet_cpu.c): the product's host engine plans every
+    install, this checker's scalar encoder fills the pending b64enc sites, all on `threads` host
+    threads.  ``product_lib`` is the loaded libkvedge_b200.so (its kv_release_* entries are handed
+    over as function pointers).  Returns (stream bytes object view, offsets)."""
+    c = ctypes
+    api = (c.c_void_p * 6)(*[c.cast(getattr(product_lib, nm), c.c_void_p).value for nm in (
+        "kv_release_plan", "kv_release_pending_count", "kv_release_pending_input", "kv_release_pending_fill",
+        "kv_release_manifest", "kv_release_free")])
+    out = c.c_void_p()
+    off = np.zeros(n + 1, dtype=np.int64)
+    rc = lib().oracle_fleet_render_cpu(c.cast(api, c.c_void_p), chart_handle, n, c.cast(names_arr, c.c_void_p), namespace,
+                                       c.cast(overrides_arr, c.c_void_p), threads, c.byref(out), off.ctypes.data)
+    if rc:
+        raise RuntimeError("oracle_fleet_render_cpu failed")
+    return out, off

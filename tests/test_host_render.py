@@ -250,3 +250,32 @@ def test_multi_document_template_files_split_like_helm(tmp_path):
                    # newline in front of it any more and stays in the document (Go regexp semantics)
                    src + b"---\nkind: Pod\n" +
                    src + b"kind: IngressClass\n" + src + b"# next\nkind: Ingress\n")
+
+
+def test_cpu_twin_of_the_fleet_render_matches_the_oracle():
+    """oracle/fleet_cpu.c (bench.py's `render_e2e` comparator: the product's engine plans, the
+    checker's scalar encoder fills the b64enc sites, on host threads) yields, per install, exactly
+    the oracle's `helm template` stream of the reference chart."""
+    import ctypes as C
+    from kvedge_b200 import _lib
+    n = 24
+    rel = [(f"chart-{i}", {"blobs": {"azIotEdgeConfig": workload.config_toml(i)} if i % 3 else {},
+                           "set": [f"nameOverride=site-{i:03d},publicSshKey={workload.ssh_key(i).decode()}"]})
+           for i in range(n)]
+    chart = helm.Chart(REF_CHART)
+    ovs = [helm._Overrides(**kw) for _, kw in rel]
+    arr = (_lib.KvOverrides * n)(*[o.struct for o in ovs])
+    names = (C.c_char_p * n)(*[nm.encode() for nm, _ in rel])
+    out, off = ob64.fleet_render_cpu(_lib.lib(), chart._h, n, names, b"default", arr, 4)
+    try:
+        stream = C.string_at(out, int(off[-1]))
+    finally:
+        ob64.lib().oracle_free(out)
+    ch = helmref.load_chart(REF_CHART)
+    for i, (name, kw) in enumerate(rel):
+        vals = helmref.render_values(ch, kw["set"])
+        for k, v in kw["blobs"].items():
+            helmref._assign(vals, [k], v)
+        ms, _ = helmref.split_manifests(helmref.render_files(ch, vals, name))
+        ref = b"".join(b"---\n# Source: " + m.name.encode() + b"\n" + m.content + b"\n" for m in ms)
+        assert stream[int(off[i]):int(off[i + 1])] == ref, name
