@@ -101,11 +101,13 @@ __device__ __forceinline__ int block_excl_scan(int v, int *total) {
 // one tile each ("solo" tiles).  Shorter units are not worth a pipeline stage of their own (a
 // stage costs the same bookkeeping whether it holds 300 bytes or 12 KiB), so a run of consecutive
 // short units whose first bytes fall into the same window of (tile_in - small_max) input bytes
-// becomes ONE "group" tile: its span is at most tile_in bytes, and the consumer warps take whole
-// units of it in turn.  A run also ends at a plan-block boundary, which keeps the rule local.
+// becomes ONE "group" tile: its span is at most tile_in bytes, and the consumer warps share its
+// units.  A run also ends at every kMaxGroupUnits-th unit (hence at every plan-block boundary):
+// that keeps the rule local and bounds the offsets a kernel stages per tile.
 // small_max == 0 turns grouping off (the older kernels only understand solo tiles).
 __host__ __device__ inline bool group_starts_at(const int64_t *in_off, int64_t u, int small_max, int window) {
-    if (u % kPlanBlock == 0) return true;
+    static_assert(kPlanBlock % kMaxGroupUnits == 0, "a plan block is a whole number of unit runs");
+    if (u % kMaxGroupUnits == 0) return true;   // also every plan-block boundary
     if (in_off[u] - in_off[u - 1] > small_max) return true;   // the unit before is a long one
     return in_off[u] / window != in_off[u - 1] / window;
 }
@@ -428,6 +430,11 @@ namespace stream {
 
 constexpr int kStageIn = kEncTileIn;       // one tile per stage
 constexpr int kStageStride = (kStageIn + 32 + 15) / 16 * 16;  // 16 bytes of slack in front and behind
+// b64enc_groups: behind a stage's bytes sit the offsets of the units of a group tile -- in_off[u0 ..
+// u0+cnt] and out_off[u0 .. u0+cnt), each with room for one entry of alignment slack in front --
+// fetched by the producer with the tile, so that no consumer ever waits on a global load for them.
+constexpr int kOffsPart = (kMaxGroupUnits + 2) * 8;            // 528 bytes, a multiple of 16
+constexpr int kGroupStageStride = kStageStride + 2 * kOffsPart;
 constexpr int kGrabMax = 8;                // tiles taken per atomic (guided: shrinks near the end)
 
 struct StageMeta {
@@ -460,13 +467,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
         : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
     return ok != 0;
 }
-// Spin with a deadline: a protocol bug must end in a trap (reported as a launch failure),
-// never in a hung GPU.
+// Wait with a deadline: a protocol bug must end in a trap (reported as a launch failure), never
+// in a hung GPU.  A waiting warp SLEEPS between polls: these kernels are bound by instruction
+// issue, and on short units two fifths of all issued instructions were polls of warps with
+// nothing to do (the producer ahead of its ring, consumers ahead of the producer).
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
-    while (!mbar_try_wait(bar, parity))
+    unsigned ns = 32;
+    while (!mbar_try_wait(bar, parity)) {
+        __nanosleep(ns);
+        if (ns < 256) ns *= 2;
         if (clock64() - t0 > 8000000000ll) __trap();
+    }
 }
 // The same on 32-bit shared addresses computed once per kernel (the pointer forms make the
 // compiler rebuild the shared-window address around every call).
@@ -482,12 +495,20 @@ __device__ __forceinline__ bool mbar_try_wait_a(uint32_t bar, uint32_t parity) {
         : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     return ok != 0;
 }
+template <unsigned kFirstNs = 32, unsigned kMaxNs = 256>
 __device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
     if (mbar_try_wait_a(bar, parity)) return;
     const long long t0 = clock64();
-    while (!mbar_try_wait_a(bar, parity))
+    unsigned ns = kFirstNs;
+    while (!mbar_try_wait_a(bar, parity)) {
+        __nanosleep(ns);
+        if (ns < kMaxNs) ns *= 2;
         if (clock64() - t0 > 8000000000ll) __trap();
+    }
 }
+// A producer waits for a ring slot, which takes a consumer microseconds to free, and is several
+// tiles ahead: it can sleep long.
+__device__ __forceinline__ void mbar_wait_slot(uint32_t bar, uint32_t parity) { mbar_wait_a<256, 2048>(bar, parity); }
 __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
@@ -506,8 +527,12 @@ __device__ __forceinline__ void encode_stage(const uint8_t *buf, uint32_t sh, ch
     // Group g starts at byte 3g + sh4 of the lane's four words; the selectors are uniform.
     auto sel_of = [](uint32_t o) { return (o << 12) | ((o + 1) << 8) | ((o + 2) << 4) | (o + 2); };
     const uint32_t sel0 = sel_of(sh4), sel1 = sel_of(sh4 - 1u), sel2 = sel_of(sh4 + 2u), sel3 = sel_of(sh4 + 1u);
-    for (int off = cw * 384 + lane * 12; off < len;
-         off += 384 * kConsumerWarps, wp += 96 * kConsumerWarps, q += 512 * kConsumerWarps) {
+    // Warp-iterations whose 32 lanes all hold 12 whole bytes run the plain body; the one iteration
+    // that meets the end of the stage (if this warp owns it) is peeled off behind the loop, so the
+    // plain body carries no end-of-unit test, and the lanes of that last iteration share ONE masked
+    // encode instead of diverging into a second copy of the whole mapping.
+    int ob = cw * 384;   // first byte of this warp's current iteration
+    for (; ob + 384 <= len; ob += 384 * kConsumerWarps, wp += 96 * kConsumerWarps, q += 512 * kConsumerWarps) {
         uint32_t a0 = wp[0], a1 = wp[1], a2 = wp[2], a3 = 0;
         if (SHIFTED) a3 = wp[3];
         if (SHIFTED && !SELP) {
@@ -515,14 +540,37 @@ __device__ __forceinline__ void encode_stage(const uint8_t *buf, uint32_t sh, ch
             a1 = __funnelshift_r(a1, a2, s8);
             a2 = __funnelshift_r(a2, a3, s8);
         }
-        const int left = len - off;
-        if (left >= 12) {
-            uint4 v;
-            if (SHIFTED && SELP)
-                v = encode_groups<NLUT>(__byte_perm(a0, a1, sel0), __byte_perm(a1, a2, sel1),
-                                        __byte_perm(a1, a2, sel2), __byte_perm(a2, a3, sel3), lut);
-            else
-                v = encode12_mixed<NLUT>(a0, a1, a2, lut);
+        uint4 v;
+        if (SHIFTED && SELP)
+            v = encode_groups<NLUT>(__byte_perm(a0, a1, sel0), __byte_perm(a1, a2, sel1),
+                                    __byte_perm(a1, a2, sel2), __byte_perm(a2, a3, sel3), lut);
+        else
+            v = encode12_mixed<NLUT>(a0, a1, a2, lut);
+        if (VEC16) {
+            *reinterpret_cast<uint4 *>(q) = v;
+        } else {
+            uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
+            q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
+        }
+    }
+    const int left = len - ob - lane * 12;   // bytes from this lane's item to the end of the stage
+    if (ob < len && left > 0) {
+        uint32_t a0 = wp[0], a1 = wp[1], a2 = wp[2];
+        if (SHIFTED) {
+            const uint32_t a3 = wp[3];
+            a0 = __funnelshift_r(a0, a1, s8);
+            a1 = __funnelshift_r(a1, a2, s8);
+            a2 = __funnelshift_r(a2, a3, s8);
+        }
+        const int nb = left < 12 ? left : 12;
+        if (nb < 12) {   // the lane holding the end: drop the bytes behind it
+            const uint32_t keep = 0xFFFFFFFFu >> (8 * (3 - ((nb - 1) & 3)));
+            if (nb <= 4) { a0 &= keep; a1 = 0u; a2 = 0u; }
+            else if (nb <= 8) { a1 &= keep; a2 = 0u; }
+            else { a2 &= keep; }
+        }
+        const uint4 v = encode12_mixed<(NLUT < 0 ? 0 : NLUT)>(a0, a1, a2, lut);
+        if (nb == 12) {
             if (VEC16) {
                 *reinterpret_cast<uint4 *>(q) = v;
             } else {
@@ -530,18 +578,8 @@ __device__ __forceinline__ void encode_stage(const uint8_t *buf, uint32_t sh, ch
                 q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
             }
         } else {
-            if (SHIFTED && SELP) {
-                a0 = __funnelshift_r(a0, a1, s8);
-                a1 = __funnelshift_r(a1, a2, s8);
-                a2 = __funnelshift_r(a2, a3, s8);
-            }
-            const uint32_t keep = 0xFFFFFFFFu >> (8 * (3 - ((left - 1) & 3)));
-            if (left <= 4) { a0 &= keep; a1 = 0u; a2 = 0u; }
-            else if (left <= 8) { a1 &= keep; a2 = 0u; }
-            else { a2 &= keep; }
-            const uint4 v = encode12(a0, a1, a2);
             uint32_t w[4] = {v.x, v.y, v.z, v.w};
-            const int rem = left % 3, gi = left / 3;
+            const int rem = nb % 3, gi = nb / 3;
             if (rem) {
 #pragma unroll
                 for (int g = 0; g < 4; ++g)
@@ -549,7 +587,7 @@ __device__ __forceinline__ void encode_stage(const uint8_t *buf, uint32_t sh, ch
                         w[g] = (rem == 1) ? ((w[g] & 0x0000FFFFu) | 0x3D3D0000u)
                                           : ((w[g] & 0x00FFFFFFu) | 0x3D000000u);
             }
-            const int nwords = (left + 2) / 3;
+            const int nwords = (nb + 2) / 3;
             uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
 #pragma unroll
             for (int g = 0; g < 4; ++g)
@@ -732,6 +770,9 @@ struct __align__(16) EncMeta {
     int64_t in_pos;      // where the stage's first byte sits in the input blob
     int unit;            // group tile: first unit and how many
     int count;
+    uint32_t offs;       // group tile: bit 2 = the units' offsets are staged behind the bytes;
+                         // bit 0 / bit 1 = the in_off / out_off copy starts one entry early
+    uint32_t pad_;
 };
 
 __device__ __forceinline__ uint32_t pinned_u32(uint32_t a) {
@@ -783,6 +824,156 @@ __device__ __noinline__ void encode_group_tile(const uint8_t *__restrict__ in, c
     }
 }
 
+// encode_group_tile with the units' offsets already in shared memory (staged by the producer with
+// the tile): a unit's three offsets are broadcast reads, nobody waits on a global load.
+//   s_in[k] = in_off[u0 + k] (k = 0..cnt), s_out[k] = out_off[u0 + k] (k = 0..cnt-1).
+template <int kConsumerWarps, int NLUT>
+__device__ __noinline__ void encode_group_staged(char *__restrict__ out, const uint8_t *buf, uint32_t sh, int64_t tpos,
+                                                 int cnt, int len, const int64_t *s_in, const int64_t *s_out,
+                                                 int cw, int lane, const uint16_t *lut) {
+    // cw: the caller rotates it from tile to tile, so that a tile of six units does not give the
+    // same two warps two units every time
+    for (int k = cw; k < cnt; k += kConsumerWarps) {
+        const int64_t a = s_in[k];
+        const int ulen = (int)(s_in[k + 1] - a);
+        if (ulen <= 0 || a < tpos || a + ulen > tpos + len) continue;   // empty; or offsets that are not sorted
+        char *udst = out + s_out[k];
+        const uint32_t ual = (uint32_t)(reinterpret_cast<uintptr_t>(udst) & 15u);
+        const uint32_t bo = sh + (uint32_t)(a - tpos);
+        const uint8_t *ubuf = buf + (bo & ~15u);
+        const uint32_t ush = bo & 15u;
+        if (ual & 3u) {   // a destination words cannot reach: bytes, from the staged copy
+            for (int off = lane * 12; off < ulen; off += 384)
+                encode_bytes(buf + bo + off, udst + off / 3 * 4, (ulen - off) < 12 ? (ulen - off) : 12);
+        } else if (ual == 0) {
+            if (ush & 3u) encode_stage<true, true, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
+            else encode_stage<true, false, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
+        } else {
+            if (ush & 3u) encode_stage<false, true, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
+            else encode_stage<false, false, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
+        }
+    }
+}
+
+// A group tile whose unit offsets were staged with it: the tile's units are treated as ONE run of
+// 12-byte items (unit k contributes ceil(len_k / 12) of them) and consumer warp cw takes
+// warp-iterations cw, cw + kConsumerWarps, ... of that run, 32 items each, wherever the unit
+// boundaries fall.  Compared with one warp per unit (encode_group_tile) no lane idles in a unit's
+// last, partial iteration (a 2006-byte cloud-init text is 5.2 iterations), a warp's per-unit
+// set-up shrinks to three broadcast reads from shared memory, and an iteration that lies inside
+// one unit -- most of them -- runs the same code as a long unit's.  In an iteration that crosses a
+// boundary every lane gets its own (source, destination, bytes left); the lane holding a unit's
+// last item masks, pads with '=' and stores only the words it owns.
+//   s_in[k] = in_off[u0 + k] (k = 0..cnt), s_out[k] = out_off[u0 + k] (k = 0..cnt-1), shared memory.
+template <int kConsumerWarps, int NLUT>
+__device__ __noinline__ void encode_group_flat(char *__restrict__ out, const uint8_t *buf, uint32_t sh, int64_t tpos,
+                                               int cnt, int len, const int64_t *s_in, const int64_t *s_out,
+                                               int cw, int lane, const uint16_t *lut) {
+    // items of a unit: ceil(ulen / 12); units whose offsets are not sorted inside the tile get none
+    auto unit_items = [&](int64_t a, int64_t b) -> int {
+        const int64_t ulen = b - a;
+        if (ulen <= 0 || a < tpos || b > tpos + len) return 0;
+        return (int)(((uint32_t)ulen + 11u) / 12u);
+    };
+    int k = 0;                                   // the unit holding this warp's next item ...
+    int64_t ua = s_in[0], ub = s_in[1];
+    int un = unit_items(ua, ub), ustart = 0;     // ... its items, and the index of its first one
+    for (int item0 = cw * 32;; item0 += 32 * kConsumerWarps) {
+        while (item0 >= ustart + un) {           // warp-uniform walk
+            ustart += un;
+            if (++k >= cnt) return;
+            ua = ub;
+            ub = s_in[k + 1];
+            un = unit_items(ua, ub);
+        }
+        const int first = item0 - ustart;        // item of unit k this iteration starts with
+        if (un - first > 32 || (un - first == 32 && (int)(ub - ua) - 12 * (first + 31) == 12)) {
+            // ---- all 32 lanes inside unit k, every item whole: a long unit's inner loop
+            const uint32_t so = sh + (uint32_t)(ua - tpos) + 12u * (uint32_t)(first + lane);
+            const uint32_t *wp = reinterpret_cast<const uint32_t *>(buf + (so & ~3u));
+            const uint32_t s8 = (so & 3u) * 8;
+            uint32_t a0 = wp[0], a1 = wp[1], a2 = wp[2];
+            if (s8) {                            // uniform: every lane of a unit has the same phase
+                const uint32_t a3 = wp[3];
+                a0 = __funnelshift_r(a0, a1, s8);
+                a1 = __funnelshift_r(a1, a2, s8);
+                a2 = __funnelshift_r(a2, a3, s8);
+            }
+            const uint4 v = encode12_mixed<NLUT>(a0, a1, a2, lut);
+            char *q = out + s_out[k] + 16 * (int64_t)(first + lane);
+            const uint32_t qa = (uint32_t)(reinterpret_cast<uintptr_t>(q) & 15u);
+            if (qa == 0) {
+                *reinterpret_cast<uint4 *>(q) = v;
+            } else if ((qa & 3u) == 0) {
+                uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
+                q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
+            } else {
+                store_chars(q, v, 16);
+            }
+            continue;
+        }
+        // ---- the iteration meets the end of unit k: lanes are handed out unit by unit
+        uint32_t so = 0;
+        char *q = nullptr;
+        int left = 0;                            // bytes of its unit from this lane's item on; <= 0: idle lane
+        {
+            int assigned = 0, kk = k, f = first, n_items = un;
+            int64_t a = ua, b = ub;
+            for (;;) {
+                const int take = n_items - f < 32 - assigned ? n_items - f : 32 - assigned;
+                if (lane >= assigned && lane < assigned + take) {
+                    const int it = f + lane - assigned;
+                    so = sh + (uint32_t)(a - tpos) + 12u * (uint32_t)it;
+                    q = out + s_out[kk] + 16 * (int64_t)it;
+                    left = (int)(b - a) - 12 * it;
+                }
+                assigned += take;
+                if (assigned >= 32 || ++kk >= cnt) break;
+                a = b;
+                b = s_in[kk + 1];
+                n_items = unit_items(a, b);
+                f = 0;
+            }
+        }
+        if (left <= 0) continue;                 // (divergent from here on: a boundary iteration)
+        const uint32_t *wp = reinterpret_cast<const uint32_t *>(buf + (so & ~3u));
+        const uint32_t s8 = (so & 3u) * 8;
+        uint32_t a0 = wp[0], a1 = wp[1], a2 = wp[2];
+        const uint32_t a3 = wp[3];
+        a0 = __funnelshift_r(a0, a1, s8);
+        a1 = __funnelshift_r(a1, a2, s8);
+        a2 = __funnelshift_r(a2, a3, s8);
+        const int nb = left < 12 ? left : 12;    // bytes of this item
+        if (nb < 12) {                           // the unit's last item: drop the bytes behind it
+            const uint32_t keep = 0xFFFFFFFFu >> (8 * (3 - ((nb - 1) & 3)));
+            if (nb <= 4) { a0 &= keep; a1 = 0u; a2 = 0u; }
+            else if (nb <= 8) { a1 &= keep; a2 = 0u; }
+            else { a2 &= keep; }
+        }
+        const uint4 v = encode12_mixed<NLUT>(a0, a1, a2, lut);
+        uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        const int rem = nb % 3, gi = nb / 3;
+        if (rem) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+                if (g == gi)
+                    w[g] = (rem == 1) ? ((w[g] & 0x0000FFFFu) | 0x3D3D0000u) : ((w[g] & 0x00FFFFFFu) | 0x3D000000u);
+        }
+        const uint32_t qa = (uint32_t)(reinterpret_cast<uintptr_t>(q) & 15u);
+        if (nb == 12 && qa == 0) {
+            *reinterpret_cast<uint4 *>(q) = make_uint4(w[0], w[1], w[2], w[3]);
+        } else if ((qa & 3u) == 0) {
+            const int nwords = (nb + 2) / 3;
+            uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+                if (g < nwords) q4[g] = w[g];
+        } else {
+            store_chars(q, make_uint4(w[0], w[1], w[2], w[3]), (nb + 2) / 3 * 4);
+        }
+    }
+}
+
 // One block per SM (or two) holding kGroups independent pipelines -- a producer warp, a ring
 // and kConsumerWarps consumer warps each -- around ONE pair table.  Compared with
 // b64enc_stream (one pipeline per block) a 2.4 KB tile occupies four consumer warps instead
@@ -794,12 +985,12 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
               const TileDesc *__restrict__ desc, int *__restrict__ header,
               const int64_t *__restrict__ in_off, int64_t n_units) {
     constexpr int kGroupWarps = 1 + kConsumerWarps;
-    constexpr int kGroupBytes = kRing > 0 ? kRing : kStages * kStageStride;
+    constexpr int kGroupBytes = kRing > 0 ? kRing : kStages * kGroupStageStride;
     static_assert(kRing == 0 || (kRing % 16 == 0 && kRing >= kStageStride), "ring must hold one full tile");
     extern __shared__ __align__(128) uint8_t dyn_smem[];
     __shared__ __align__(8) uint64_t full_bar[kGroups][kStages];
     __shared__ __align__(8) uint64_t empty_bar[kGroups][kStages];
-    __shared__ EncMeta meta[kGroups][kStages];
+    __shared__ __align__(16) EncMeta meta[kGroups][kStages];
     __shared__ uint32_t ring_start[kGroups][kStages];  // producer only: where each in-flight tile starts
     __shared__ uint16_t lut[NLUT > 0 ? 4096 : 1];
 
@@ -819,6 +1010,8 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
     pdl_wait();   // everything above overlapped the plan; the tile table is read from here on
     const uint32_t full_a = pinned_u32(smem_u32(&full_bar[grp][0])), empty_a = pinned_u32(smem_u32(&empty_bar[grp][0]));
 
+    const int64_t *out_off = reinterpret_cast<const int64_t *>(
+        ((unsigned long long)(unsigned)header[5] << 32) | (unsigned long long)(unsigned)header[4]);
     if (role == 0) {
         // ------------------------------------------------------------------ producer
         const int n_tiles = header[0];
@@ -861,12 +1054,12 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
                 const bool bulk_ok = in_pos >= 16 && in_pos + len + 16 <= in_end && (dalign & 3u) == 0;
                 const uint32_t s = c % kStages;
                 const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
-                uint32_t boff = s * kStageStride;
+                uint32_t boff = s * kGroupStageStride;
                 if (kRing == 0) {
-                    mbar_wait_a(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
+                    mbar_wait_slot(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
                 } else {
                     while (waited + kStages <= c) {   // the barrier pair itself
-                        mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                        mbar_wait_slot(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                         ++waited;
                     }
                     // room for this tile (+ the 16 bytes a lane may read past its last byte)
@@ -880,7 +1073,7 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
                         } else if (head + need <= tail) {                         // in flight: [tail, end) + [0, head)
                             break;
                         }
-                        mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                        mbar_wait_slot(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                         ++waited;
                     }
                     boff = head;
@@ -895,11 +1088,38 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
                 m.in_pos = in_pos;
                 m.unit = unit;
                 m.count = ucount;
+                m.offs = 0;
+                m.pad_ = 0;
+                // a group tile's unit offsets ride along (16-byte pieces of the two offset arrays
+                // that cover the entries needed; never a byte outside either array)
+                uint32_t bytes_i = 0, bytes_o = 0;
+                const char *src_i = nullptr, *src_o = nullptr;
+                if (kRing == 0 && is_group && bulk_ok && ucount <= kMaxGroupUnits) {
+                    const char *pi = reinterpret_cast<const char *>(in_off + unit);
+                    const char *po = reinterpret_cast<const char *>(out_off + unit);
+                    const uint32_t ai = (uint32_t)(reinterpret_cast<uintptr_t>(pi) & 15u);
+                    const uint32_t ao = (uint32_t)(reinterpret_cast<uintptr_t>(po) & 15u);
+                    bytes_i = (ai + 8u * (uint32_t)(ucount + 1) + 15u) & ~15u;
+                    bytes_o = (ao + 8u * (uint32_t)ucount + 15u) & ~15u;
+                    src_i = pi - ai;
+                    src_o = po - ao;
+                    const char *end_i = reinterpret_cast<const char *>(in_off + n_units + 1);
+                    const char *end_o = reinterpret_cast<const char *>(out_off + n_units + 1);
+                    const bool fits = src_i >= reinterpret_cast<const char *>(in_off) && src_i + bytes_i <= end_i &&
+                                      src_o >= reinterpret_cast<const char *>(out_off) && src_o + bytes_o <= end_o &&
+                                      ((ai | ao) & 7u) == 0;
+                    if (fits) m.offs = 4u | (ai >> 3) | ((ao >> 3) << 1);
+                    else bytes_i = bytes_o = 0;
+                }
                 meta[grp][s] = m;
                 if (bulk_ok) {
                     const uint32_t bytes = (sh + (uint32_t)len + 15u) & ~15u;
-                    mbar_arrive_expect_tx(&full_bar[grp][s], bytes);
+                    mbar_arrive_expect_tx(&full_bar[grp][s], bytes + bytes_i + bytes_o);
                     bulk_g2s(ring + boff, src - sh, bytes, &full_bar[grp][s]);
+                    if (bytes_i) {
+                        bulk_g2s(ring + boff + kStageStride, src_i, bytes_i, &full_bar[grp][s]);
+                        bulk_g2s(ring + boff + kStageStride + kOffsPart, src_o, bytes_o, &full_bar[grp][s]);
+                    }
                 } else {
                     mbar_arrive(&full_bar[grp][s]);
                 }
@@ -913,10 +1133,10 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
             // end-of-work stage, seen by every consumer warp of the group
             const uint32_t s = c % kStages;
             if (kRing == 0) {
-                mbar_wait_a(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
+                mbar_wait_slot(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
             } else {
                 while (waited + kStages <= c) {
-                    mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                    mbar_wait_slot(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                     ++waited;
                 }
             }
@@ -933,9 +1153,8 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
         // ------------------------------------------------------------------ consumers
         const int cw = role - 1;
         const EncMeta *gmeta = meta[grp];
-        const int64_t *out_off = reinterpret_cast<const int64_t *>(
-            ((unsigned long long)(unsigned)header[5] << 32) | (unsigned long long)(unsigned)header[4]);
         uint32_t s = 0, ph = 0;
+        int rr = 0;
         for (;;) {
             mbar_wait_a(full_a + s * 8u, ph);
             const int4 hot = *reinterpret_cast<const int4 *>(&gmeta[s]);
@@ -945,8 +1164,19 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
             const uint8_t *buf = ring + (info >> 12);
             char *dst = reinterpret_cast<char *>(((uint64_t)(uint32_t)hot.y << 32) | (uint32_t)hot.x);
             if (info & 0x400u) {
-                encode_group_tile<kConsumerWarps, NLUT>(in, in_off, out, out_off, buf, sh, (info & 0x200u) == 0, gmeta[s].in_pos,
-                                                        gmeta[s].unit, gmeta[s].count, len, cw, lane, lut);
+                // units go round the consumer warps ACROSS tiles (rr: units seen so far, mod warps)
+                const uint32_t offs = gmeta[s].offs;
+                const int ucnt = gmeta[s].count;
+                const int rcw = (cw + kConsumerWarps - rr) % kConsumerWarps;
+                if (offs & 4u)
+                    encode_group_staged<kConsumerWarps, NLUT>(out, buf, sh, gmeta[s].in_pos, ucnt, len,
+                                                            reinterpret_cast<const int64_t *>(buf + kStageStride) + (offs & 1u),
+                                                            reinterpret_cast<const int64_t *>(buf + kStageStride + kOffsPart) + ((offs >> 1) & 1u),
+                                                            rcw, lane, lut);
+                else
+                    encode_group_tile<kConsumerWarps, NLUT>(in, in_off, out, out_off, buf, sh, (info & 0x200u) == 0, gmeta[s].in_pos,
+                                                            gmeta[s].unit, ucnt, len, rcw, lane, lut);
+                rr = (rr + ucnt) % kConsumerWarps;
             } else if (info & 0x200u) {
                 const uint8_t *src = in + gmeta[s].in_pos;
                 for (int off = cw * 384 + lane * 12; off < len; off += 384 * kConsumerWarps)
@@ -1366,11 +1596,11 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                 const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
                 uint32_t boff = s * kDecStageStride;
                 if (kRing == 0) {
-                    mbar_wait_a(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
+                    mbar_wait_slot(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
                 } else {
                     // the barrier pair itself: tile c - kStages must be finished
                     while (waited + kStages <= c) {
-                        mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                        mbar_wait_slot(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                         ++waited;
                     }
                     // room for this tile (+ the 16-byte chunk a lane may read past its last character)
@@ -1384,7 +1614,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                         } else if (head + need <= tail) {                         // in flight: [tail, end) + [0, head)
                             break;
                         }
-                        mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                        mbar_wait_slot(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                         ++waited;
                     }
                     boff = head;
@@ -1416,10 +1646,10 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
         if (lane == 0) {
             const uint32_t s = c % kStages;
             if (kRing == 0) {
-                mbar_wait_a(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
+                mbar_wait_slot(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
             } else {
                 while (waited + kStages <= c) {
-                    mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                    mbar_wait_slot(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                     ++waited;
                 }
             }
@@ -1442,6 +1672,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
         const int64_t *out_off = reinterpret_cast<const int64_t *>(
             ((unsigned long long)(unsigned)header[5] << 32) | (unsigned long long)(unsigned)header[4]);
         uint32_t s = 0, ph = 0;
+        int rr = 0;
         for (;;) {
             mbar_wait_a(full_a + s * 8u, ph);
             const int4 hot = *reinterpret_cast<const int4 *>(&gmeta[s]);
@@ -1456,7 +1687,9 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                 const int u0 = gmeta[s].unit, cnt = gmeta[s].count;
                 const uint8_t *tsrc = gmeta[s].src;
                 const int64_t tpos = tsrc - reinterpret_cast<const uint8_t *>(in);
-                for (int j = cw; j < cnt; j += kConsumerWarps) {
+                const int rcw = (cw + kConsumerWarps - rr) % kConsumerWarps;   // units go round the warps across tiles
+                rr = (rr + cnt) % kConsumerWarps;
+                for (int j = rcw; j < cnt; j += kConsumerWarps) {
                     const int u = u0 + j;
                     const int64_t a = in_off[u];
                     const int ulen = (int)(in_off[u + 1] - a);
@@ -1723,7 +1956,7 @@ using EncKernel = void (*)(const uint8_t *, char *, const TileDesc *, int *, con
 struct EncGroupVariant {
     EncKernel fn; int groups, stages, consumers, ring;
     int threads() const { return 32 * groups * (1 + consumers); }
-    size_t dyn() const { return (size_t)groups * (ring ? (size_t)ring : (size_t)stages * stream::kStageStride); }
+    size_t dyn() const { return (size_t)groups * (ring ? (size_t)ring : (size_t)stages * stream::kGroupStageStride); }
 };
 static const EncGroupVariant kEncGroup[] = {
     {stream::b64enc_groups<5, 3, 4, 2, 1, 0>, 5, 3, 4, 0},   // product

@@ -19,6 +19,7 @@ int dec_tile_in();
 int dec_small_max();   // units up to this many characters are grouped into shared tiles (0: never)
 constexpr int kThreads = 256;
 constexpr int kPlanBlock = 1024;  // units per block in the plan kernels
+constexpr int kMaxGroupUnits = 64;  // most units one group tile may hold (see plan_count)
 
 // One tile of work: a contiguous piece of one unit.
 struct __align__(32) TileDesc {
