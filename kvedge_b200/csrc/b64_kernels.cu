@@ -501,8 +501,10 @@ __device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
     const long long t0 = clock64();
     unsigned ns = kFirstNs;
     while (!mbar_try_wait_a(bar, parity)) {
-        __nanosleep(ns);
-        if (ns < kMaxNs) ns *= 2;
+        if (kMaxNs > 0) {
+            __nanosleep(ns);
+            if (ns < kMaxNs) ns *= 2;
+        }
         if (clock64() - t0 > 8000000000ll) __trap();
     }
 }
@@ -1596,11 +1598,11 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                 const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
                 uint32_t boff = s * kDecStageStride;
                 if (kRing == 0) {
-                    mbar_wait_slot(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
+                    mbar_wait_a<0, 0>(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
                 } else {
                     // the barrier pair itself: tile c - kStages must be finished
                     while (waited + kStages <= c) {
-                        mbar_wait_slot(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                        mbar_wait_a<0, 0>(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                         ++waited;
                     }
                     // room for this tile (+ the 16-byte chunk a lane may read past its last character)
@@ -1614,7 +1616,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                         } else if (head + need <= tail) {                         // in flight: [tail, end) + [0, head)
                             break;
                         }
-                        mbar_wait_slot(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                        mbar_wait_a<0, 0>(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                         ++waited;
                     }
                     boff = head;
@@ -1646,10 +1648,10 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
         if (lane == 0) {
             const uint32_t s = c % kStages;
             if (kRing == 0) {
-                mbar_wait_slot(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
+                mbar_wait_a<0, 0>(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
             } else {
                 while (waited + kStages <= c) {
-                    mbar_wait_slot(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                    mbar_wait_a<0, 0>(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                     ++waited;
                 }
             }
@@ -1672,9 +1674,8 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
         const int64_t *out_off = reinterpret_cast<const int64_t *>(
             ((unsigned long long)(unsigned)header[5] << 32) | (unsigned long long)(unsigned)header[4]);
         uint32_t s = 0, ph = 0;
-        int rr = 0;
         for (;;) {
-            mbar_wait_a(full_a + s * 8u, ph);
+            mbar_wait_a<0, 0>(full_a + s * 8u, ph);
             const int4 hot = *reinterpret_cast<const int4 *>(&gmeta[s]);
             const int len = hot.z;
             if (len < 0) break;
@@ -1687,9 +1688,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                 const int u0 = gmeta[s].unit, cnt = gmeta[s].count;
                 const uint8_t *tsrc = gmeta[s].src;
                 const int64_t tpos = tsrc - reinterpret_cast<const uint8_t *>(in);
-                const int rcw = (cw + kConsumerWarps - rr) % kConsumerWarps;   // units go round the warps across tiles
-                rr = (rr + cnt) % kConsumerWarps;
-                for (int j = rcw; j < cnt; j += kConsumerWarps) {
+                for (int j = cw; j < cnt; j += kConsumerWarps) {
                     const int u = u0 + j;
                     const int64_t a = in_off[u];
                     const int ulen = (int)(in_off[u + 1] - a);
