@@ -70,3 +70,16 @@ def test_product_library_reads_no_environment_knob():
     assert b"KVEDGE_" not in raw
     # exactly the product kernels: one grouped encoder, the tiny-batch encoder, one decoder
     assert raw.count(b"b64enc_groupsILi") > 0 and b"b64enc_streamILi3ELi8ELin1" not in raw
+
+
+def test_no_hot_path_record_is_machine_readable():
+    """BASELINE.json's north_star asks for the repo to be flagged NO_HOT_PATH: the flag is a JSON
+    record at the repo root, and the numbers it quotes are the committed measurements."""
+    import json
+    rec = json.load(open(os.path.join(ROOT, "NO_HOT_PATH.json")))
+    assert rec["verdict"] == "NO_HOT_PATH" and rec["negative_inventory"]["lines_of_program_code"] == 0
+    lat = json.load(open(os.path.join(ROOT, "profiles", "r01_single_install_latency.json")))
+    one = rec["measured_at_the_references_own_size"]["one_install"]
+    assert one["b64enc_2KB"]["gpu_us"] == lat["gpu_b64enc_2KB_us"]
+    assert one["b64enc_2KB"]["cpu_one_core_us"] == lat["cpu_oracle_b64enc_2KB_us"]
+    assert one["b64enc_11KB"]["gpu_us"] == lat["gpu_b64enc_11KB_us"]
