@@ -205,6 +205,7 @@ void render_files(const kv_chart *c, const Value &vals, const char *release, con
     opt.defer_b64 = defer;
     opt.pending = pending;
     opt.values_outlive_pending = keepalive != nullptr;
+    opt.session_id = TemplateSet::next_session_id();   // one release, one value tree: includes may be memoised
     if (keepalive) *keepalive = top;
     opt.encode = gpu_encode_one;
     opt.decode = gpu_decode_one;
@@ -378,6 +379,7 @@ int kv_chart_load(const char *chart_dir, kv_chart **out) {
             c->ts.parse(prefix + t.first, t.second);
             if (TemplateSet::has_sentinel_bytes(t.second)) c->templates_have_sentinels = true;
         }
+        c->ts.finalize();
         prepare_chart(c.get());
         *out = c.release();
         return KV_OK;

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
 #include <deque>
 #ifdef __SSE2__
 #include <emmintrin.h>
@@ -244,6 +245,7 @@ struct Pipeline {
     bool defer_candidate = false;   // `<two or more commands> | b64enc`, no variable: may stay pending
 };
 struct Var { const std::string *name; Value v; };
+struct IncludeMemo { const NodeList *body; const Map *dot; std::string text; };
 struct Node {
     enum Kind { Text, Action, If, With, Range, Template } kind = Text;
     std::string text;                 // Text payload / Template name
@@ -929,6 +931,7 @@ struct Exec {
     // function, the dot of a `with $x`) stay valid while later variables come and go.
     std::deque<Var> &vars;
     std::vector<std::string> &capture_pool;   // spare buffers for include
+    std::vector<IncludeMemo> *memo;           // this release's memoised includes, or null
     size_t frame_base = 0;      // variables below this belong to the caller of include/template
 
     static const std::string &dollar() { static const std::string d = "$"; return d; }
@@ -991,6 +994,19 @@ struct Exec {
         switch (fn) {
         case F_include: {
             need(2);
+            // same template, same (immutable) dot, no way to see .Template: same text as last time
+            const NodeList *body = nullptr;
+            if (memo && a[0].kind == Value::String && a[1].kind == Value::MapK) {
+                auto it = ts.templates_.find(a[0].s);
+                if (it != ts.templates_.end()) {
+                    auto ok = ts.memo_ok_.find(&it->second);
+                    if (ok != ts.memo_ok_.end() && ok->second) {
+                        body = &it->second;
+                        for (const auto &m : *memo)
+                            if (m.body == body && m.dot == a[1].map.get()) return Value::str(m.text);
+                    }
+                }
+            }
             std::string buf;
             if (!capture_pool.empty()) { buf = std::move(capture_pool.back()); capture_pool.pop_back(); buf.clear(); }
             ++capture_depth;
@@ -1002,6 +1018,7 @@ struct Exec {
                 throw;
             }
             --capture_depth;
+            if (body) memo->push_back({body, a[1].map.get(), buf});
             return Value::str(std::move(buf));
         }
         case F_default:
@@ -1351,6 +1368,86 @@ void TemplateSet::parse(const std::string &name, const std::string &src) {
     templates_[name] = nodes;
 }
 
+uint64_t TemplateSet::next_session_id() {
+    static std::atomic<uint64_t> next{1};
+    return next.fetch_add(1);
+}
+
+namespace {
+
+// Can executing `nodes` depend on anything but the dot it is given?  The one thing that differs
+// between two includes of a template with the same dot inside one release is .Template (it names
+// the file being rendered), so a body is memoisable when it never reaches a field chain starting
+// at Template, never hands its whole dot to anything but a memoisable template, and only names
+// templates by string literals.
+struct Purity {
+    const std::map<std::string, NodeList> &all;
+    std::map<const NodeList *, int> state;   // 1 = in progress (assume pure: recursion), 2 = pure, 3 = impure
+
+    bool operand_ok(const Operand &op, bool whole_dot_allowed) {
+        if ((op.kind == Operand::Field) && !op.fields.empty() && op.fields[0] == "Template") return false;
+        if (op.kind == Operand::Var && op.text == "$" && !op.fields.empty() && op.fields[0] == "Template") return false;
+        if ((op.kind == Operand::Dot || (op.kind == Operand::Var && op.fields.empty())) && !whole_dot_allowed) return false;
+        if (op.kind == Operand::Paren) return pipe_ok(*op.paren);
+        return true;
+    }
+    bool cmd_ok(const Command &c) {
+        const Operand &f = c.args[0];
+        if (f.kind == Operand::Ident && f.fn == F_include) {
+            if (c.args.size() < 2 || c.args[1].kind != Operand::Str) return false;   // piped or computed name
+            auto it = all.find(c.args[1].text);
+            if (it == all.end() || !body_ok(it->second)) return false;
+            for (size_t k = 2; k < c.args.size(); ++k)
+                if (!operand_ok(c.args[k], true)) return false;
+            return true;
+        }
+        // `default`, `and`, `or`, `ternary`, `required`, `with`-style passing keep a value as it is;
+        // anything else given the whole dot could print or walk it
+        const bool passes_values = f.kind == Operand::Ident && (f.fn == F_default || f.fn == F_and || f.fn == F_or ||
+                                                                 f.fn == F_ternary || f.fn == F_required || f.fn == F_not ||
+                                                                 f.fn == F_empty || f.fn == F_hasKey);
+        for (size_t k = 0; k < c.args.size(); ++k)
+            if (!operand_ok(c.args[k], k == 0 ? c.args.size() == 1 && false : passes_values)) return false;
+        return true;
+    }
+    bool pipe_ok(const Pipeline &p) {
+        for (const auto &c : p.cmds)
+            if (!cmd_ok(c)) return false;
+        return true;
+    }
+    bool list_ok(const NodeList &nodes) {
+        for (const auto &nd : nodes) {
+            if (nd->pipe && !pipe_ok(*nd->pipe)) return false;
+            if (nd->kind == Node::Template) {
+                auto it = all.find(nd->text);
+                if (it == all.end() || !body_ok(it->second)) return false;
+            }
+            if (nd->kind == Node::With || nd->kind == Node::Range) return false;   // dot changes: keep the analysis simple
+            if (!list_ok(nd->body) || !list_ok(nd->else_body)) return false;
+        }
+        return true;
+    }
+    bool body_ok(const NodeList &nodes) {
+        int &st = state[&nodes];
+        if (st == 1 || st == 2) return true;
+        if (st == 3) return false;
+        st = 1;
+        const bool ok = list_ok(nodes);
+        state[&nodes] = ok ? 2 : 3;
+        return ok;
+    }
+};
+
+}  // namespace
+
+void TemplateSet::finalize() {
+    memo_ok_.clear();
+    for (const auto &kv : templates_) {
+        Purity p{templates_, {}};   // fresh per template: an "in progress" assumption must not leak
+        memo_ok_[&kv.second] = p.body_ok(kv.second);
+    }
+}
+
 const NodeList *TemplateSet::find(const std::string &name) const {
     auto it = templates_.find(name);
     return it == templates_.end() ? nullptr : &it->second;
@@ -1359,7 +1456,13 @@ const NodeList *TemplateSet::find(const std::string &name) const {
 void TemplateSet::execute_into(const NodeList &nodes, const Value &data, const ExecOptions &opt, std::string &out) const {
     // the variable stack and the include buffers are kept per thread: a fleet render executes the
     // same few templates thousands of times on every host thread
-    struct Scratch { std::deque<Var> vars; std::vector<std::string> pool; bool busy = false; };
+    struct Scratch {
+        std::deque<Var> vars;
+        std::vector<std::string> pool;
+        std::vector<IncludeMemo> memo;
+        uint64_t session = 0;
+        bool busy = false;
+    };
     static thread_local Scratch tls;
     std::unique_ptr<Scratch> local;   // only for a nested render from inside a callback
     if (tls.busy) local.reset(new Scratch);
@@ -1369,7 +1472,11 @@ void TemplateSet::execute_into(const NodeList &nodes, const Value &data, const E
         explicit Guard(Scratch &x) : s(x) { s.busy = true; }
         ~Guard() { s.vars.clear(); s.busy = false; }
     } guard(sc);
-    Exec ex{*this, opt, 0, sc.vars, sc.pool};
+    if (sc.session != opt.session_id) {   // another release: its values are other values
+        sc.memo.clear();
+        sc.session = opt.session_id;
+    }
+    Exec ex{*this, opt, 0, sc.vars, sc.pool, opt.session_id ? &sc.memo : nullptr};
     sc.vars.push_back({&Exec::dollar(), data});
     ex.exec_list(nodes, data, out);
 }

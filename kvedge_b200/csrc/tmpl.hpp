@@ -155,6 +155,11 @@ class TemplateSet {
         bool defer_b64 = false;             // leave top-level `... | b64enc` sites pending
         std::vector<Pending> *pending = nullptr;
         bool values_outlive_pending = false;  // the caller keeps `data` alive as long as `pending`
+        // Non-zero: all execute_into calls carrying this id render ONE release from the same
+        // (immutable) value tree; an `include` of a template that cannot see .Template is then
+        // evaluated once per (template, dot) and its text reused -- a chart calls its name helper a
+        // dozen times per release.  Ids must never repeat (take them from next_session_id()).
+        uint64_t session_id = 0;
         ImmediateEncoder encode;            // required whenever a b64enc must run now
         ImmediateEncoder decode;            // b64dec (optional)
     };
@@ -162,6 +167,11 @@ class TemplateSet {
     // The same for callers that render one template many times: look it up once, append to `out`.
     const NodeList *find(const std::string &name) const;
     void execute_into(const NodeList &nodes, const Value &data, const ExecOptions &opt, std::string &out) const;
+
+    static uint64_t next_session_id();
+    // Work out which named templates may be memoised within a release (call once, after the last
+    // parse and before templates are executed from several threads).
+    void finalize();
 
     // Placeholder protocol (render_capi.cpp expands it): 4 id bytes in [0x10,0x20), then 0x01.
     static constexpr size_t kPlaceholderLen = 5;
@@ -172,6 +182,7 @@ class TemplateSet {
   private:
     friend struct Exec;
     std::map<std::string, NodeList> templates_;
+    std::map<const NodeList *, bool> memo_ok_;   // named templates whose text depends on (name, dot) alone
 };
 
 }  // namespace tmpl
