@@ -569,6 +569,27 @@ int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *
     static std::mutex stage_mu;   // the staging buffers are one per process
     std::unique_lock<std::mutex> stage_lock(stage_mu, std::defer_lock);
 
+    constexpr int kChunkBlocks = 128;   // blocks (of kBlock installs) per GPU batch: ~1000 installs, ~14 MB of payload
+    const int n_chunks = (n_blocks + kChunkBlocks - 1) / kChunkBlocks;
+    std::vector<std::atomic<unsigned>> packed((size_t)(n_chunks > 0 ? n_chunks : 1));
+    std::vector<std::atomic<int>> encoded((size_t)(n_chunks > 0 ? n_chunks : 1));
+    for (auto &x : packed) x.store(0);
+    for (auto &x : encoded) x.store(0);
+    std::thread gpu_thread;
+    auto gpu_driver = [&]() {
+        for (int c = 0; c < n_chunks; ++c) {
+            while (packed[(size_t)c].load(std::memory_order_acquire) < n_thr) std::this_thread::yield();
+            const int i_lo = c * kChunkBlocks * kBlock, i_hi = std::min(n_releases, (c + 1) * kChunkBlocks * kBlock);
+            const size_t u_lo = unit_base[(size_t)i_lo], u_hi = unit_base[(size_t)i_hi];
+            if (u_hi > u_lo && first_rc.load() == KV_OK) {
+                int rc = kv_b64enc_batch(reinterpret_cast<const uint8_t *>(stage_in), &in_off[u_lo], (int64_t)(u_hi - u_lo), stage_out,
+                                         &enc_off[u_lo]);
+                if (rc) set_error(rc, kv_last_error());
+            }
+            encoded[(size_t)c].store(1, std::memory_order_release);
+        }
+    };
+
     auto for_my_installs = [&](unsigned t, auto fn) {
         for (int b = (int)t; b < n_blocks; b += (int)n_thr)
             for (int i = b * kBlock; i < n_releases && i < (b + 1) * kBlock; ++i) fn(i);
@@ -615,42 +636,53 @@ int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *
             else if (!(buf = out_buffer_get(total_out + 1))) set_error(KV_ENOMEM, "malloc");
         }
         barrier.wait();
-        // ---- pack
-        if (first_rc.load() == KV_OK)
-            for_my_installs(t, [&](int i) {
+        // ---- pack | encode | assemble, pipelined over chunks of installs: while the GPU (driven by
+        // one extra thread, which mostly sleeps in the driver) encodes chunk c, the team packs
+        // chunk c + 1 and assembles the chunks that are back; every thread still touches only the
+        // installs it planned, and frees them when it has assembled them
+        if (first_rc.load() != KV_OK) {
+            for_my_installs(t, [&](int i) { rel[(size_t)i].reset(); });
+            return;
+        }
+        if (t == 0) gpu_thread = std::thread(gpu_driver);
+        auto my_installs_of_chunk = [&](int c, auto fn) {
+            const int lo = c * kChunkBlocks, hi = std::min(n_blocks, (c + 1) * kChunkBlocks);
+            for (int b = lo + (int)((t + n_thr - (unsigned)(lo % (int)n_thr)) % n_thr); b < hi; b += (int)n_thr)
+                for (int i = b * kBlock; i < n_releases && i < (b + 1) * kBlock; ++i) fn(i);
+        };
+        auto assemble = [&](int c) {
+            const bool ok = first_rc.load() == KV_OK;
+            my_installs_of_chunk(c, [&](int i) {
+                if (ok) {
+                    kv_release &r = *rel[(size_t)i];
+                    const int64_t *eo = &enc_off[unit_base[(size_t)i]];
+                    expand_into(buf + man_off[(size_t)i], r.manifest, r.pending, [&](size_t id) { return stage_out + eo[id]; });
+                }
+                rel[(size_t)i].reset();
+            });
+        };
+        int next_asm = 0;
+        for (int c = 0; c < n_chunks; ++c) {
+            my_installs_of_chunk(c, [&](int i) {
                 size_t u = unit_base[(size_t)i];
                 for (auto &p : rel[(size_t)i]->pending) memcpy(stage_in + in_off[u++], p.data(), p.size());
             });
-        barrier.wait();
-        if (t == 0 && first_rc.load() == KV_OK) {
-            lap("pack inputs");
-            const int64_t n_units = (int64_t)unit_base[(size_t)n_releases];
-            if (n_units > 0) {
-                int rc = kv_b64enc_batch(reinterpret_cast<const uint8_t *>(stage_in), in_off.data(), n_units, stage_out,
-                                         enc_off.data());
-                if (rc) set_error(rc, kv_last_error());
-            }
-            lap("kv_b64enc_batch");
+            packed[(size_t)c].fetch_add(1, std::memory_order_release);
+            while (next_asm < c && encoded[(size_t)next_asm].load(std::memory_order_acquire)) assemble(next_asm++);
         }
-        barrier.wait();
-        // ---- assemble, and free what this thread planned
-        const bool ok = first_rc.load() == KV_OK;
-        for_my_installs(t, [&](int i) {
-            if (!rel[(size_t)i]) return;
-            if (ok) {
-                kv_release &r = *rel[(size_t)i];
-                const int64_t *eo = &enc_off[unit_base[(size_t)i]];
-                expand_into(buf + man_off[(size_t)i], r.manifest, r.pending, [&](size_t id) { return stage_out + eo[id]; });
-            }
-            rel[(size_t)i].reset();
-        });
+        for (; next_asm < n_chunks; ++next_asm) {
+            while (!encoded[(size_t)next_asm].load(std::memory_order_acquire)) std::this_thread::yield();
+            assemble(next_asm);
+        }
     };
     {
         std::vector<std::thread> team;
         for (unsigned t = 1; t < n_thr; ++t) team.emplace_back(team_member, t);
         team_member(0);
         for (auto &th : team) th.join();
+        if (gpu_thread.joinable()) gpu_thread.join();
     }
+    lap("pack | encode | assemble (pipelined)");
     if (first_rc.load() != KV_OK) {
         if (buf) kv_free(buf);
         return fail(first_rc.load(), err_msg);
@@ -658,7 +690,6 @@ int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *
     for (int i = 0; i <= n_releases; ++i) out_off[i] = (int64_t)man_off[(size_t)i];
     buf[total_out] = 0;
     *out = buf;
-    lap("assemble");
     return KV_OK;
 }
 
