@@ -426,6 +426,9 @@ __device__ __noinline__ void encode_bytes(const uint8_t *p, char *q, int nvalid)
 // straight to global memory.  The producer owns all scheduling (tile counter, descriptor
 // loads, alignment), so the consumers never wait on a dependent global load, and the bytes
 // in flight per SM are set by the ring depth instead of by the number of resident warps.
+#ifndef KVEDGE_GROUP_NLUT
+#define KVEDGE_GROUP_NLUT 3
+#endif
 namespace stream {
 
 constexpr int kStageIn = kEncTileIn;       // one tile per stage
@@ -829,10 +832,13 @@ __device__ __noinline__ void encode_group_tile(const uint8_t *__restrict__ in, c
 // encode_group_tile with the units' offsets already in shared memory (staged by the producer with
 // the tile): a unit's three offsets are broadcast reads, nobody waits on a global load.
 //   s_in[k] = in_off[u0 + k] (k = 0..cnt), s_out[k] = out_off[u0 + k] (k = 0..cnt-1).
-template <int kConsumerWarps, int NLUT>
+template <int kConsumerWarps, int NLUT_LONG>
 __device__ __noinline__ void encode_group_staged(char *__restrict__ out, const uint8_t *buf, uint32_t sh, int64_t tpos,
                                                  int cnt, int len, const int64_t *s_in, const int64_t *s_out,
                                                  int cw, int lane, const uint16_t *lut) {
+    // Short units leave the load/store pipe half idle and saturate the ALU pipe (per-unit set-up is
+    // all integer work), so here three of the four groups go through the pair table, not two.
+    constexpr int NLUT = NLUT_LONG > 0 ? KVEDGE_GROUP_NLUT : NLUT_LONG;
     // cw: the caller rotates it from tile to tile, so that a tile of six units does not give the
     // same two warps two units every time
     for (int k = cw; k < cnt; k += kConsumerWarps) {
