@@ -498,22 +498,33 @@ __device__ __forceinline__ bool mbar_try_wait_a(uint32_t bar, uint32_t parity) {
         : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     return ok != 0;
 }
+// try_wait with a suspend-time hint: the hardware parks the warp until the phase completes (it
+// wakes at once) or the hint (in ns) runs out, so a long wait costs a handful of instructions
+// instead of a poll every hundred nanoseconds.
+__device__ __forceinline__ bool mbar_try_wait_hint_a(uint32_t bar, uint32_t parity, uint32_t hint_ns) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity), "r"(hint_ns) : "memory");
+    return ok != 0;
+}
 template <unsigned kFirstNs = 32, unsigned kMaxNs = 256>
 __device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
+    (void)kFirstNs; (void)kMaxNs;
     if (mbar_try_wait_a(bar, parity)) return;
     const long long t0 = clock64();
-    unsigned ns = kFirstNs;
-    while (!mbar_try_wait_a(bar, parity)) {
-        if (kMaxNs > 0) {
-            __nanosleep(ns);
-            if (ns < kMaxNs) ns *= 2;
-        }
+    while (!mbar_try_wait_hint_a(bar, parity, 20000u))
         if (clock64() - t0 > 8000000000ll) __trap();
-    }
 }
-// A producer waits for a ring slot, which takes a consumer microseconds to free, and is several
-// tiles ahead: it can sleep long.
-__device__ __forceinline__ void mbar_wait_slot(uint32_t bar, uint32_t parity) { mbar_wait_a<256, 2048>(bar, parity); }
+// A producer waits for a ring slot, which takes the consumers microseconds to free.
+__device__ __forceinline__ void mbar_wait_slot(uint32_t bar, uint32_t parity) {
+    if (mbar_try_wait_a(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait_hint_a(bar, parity, 20000u))
+        if (clock64() - t0 > 8000000000ll) __trap();
+}
 __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
