@@ -530,6 +530,15 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src, uint32
                  ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// Mask keeping the n lowest bytes of a word (n <= 0: none, n >= 4: all).  PTX shifts clamp their
+// amount to the register width, so no comparison is needed.
+__device__ __forceinline__ uint32_t keep_low_bytes(int n) {
+    uint32_t m;
+    const int bits = n < 0 ? 0 : 8 * n;
+    asm("shl.b32 %0, 0xFFFFFFFF, %1;" : "=r"(m) : "r"(bits));
+    return ~m;
+}
+
 // Iterations cw, cw+8, ... of one stage (a tile of `len` input bytes at byte offset `sh` of
 // `buf`) by consumer warp cw.
 template <bool VEC16, bool SHIFTED, int kConsumerWarps, int NLUT, bool SELP>
@@ -569,8 +578,13 @@ __device__ __forceinline__ void encode_stage(const uint8_t *buf, uint32_t sh, ch
             q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
         }
     }
-    const int left = len - ob - lane * 12;   // bytes from this lane's item to the end of the stage
-    if (ob < len && left > 0) {
+    // The iteration holding the end of the stage: every lane runs the SAME code (no divergent copy
+    // of the mapping for the one lane with the end in it) -- bytes behind the end are masked off
+    // with shifts that clamp, the '=' padding is patched in with selects, and only the stores
+    // differ: a whole item leaves as one 16-byte store, the last item word by word.
+    if (ob < len) {
+        const int left = len - ob - lane * 12;   // bytes from this lane's item to the end of the stage
+        const int nb = left < 0 ? 0 : (left > 12 ? 12 : left);
         uint32_t a0 = wp[0], a1 = wp[1], a2 = wp[2];
         if (SHIFTED) {
             const uint32_t a3 = wp[3];
@@ -578,32 +592,23 @@ __device__ __forceinline__ void encode_stage(const uint8_t *buf, uint32_t sh, ch
             a1 = __funnelshift_r(a1, a2, s8);
             a2 = __funnelshift_r(a2, a3, s8);
         }
-        const int nb = left < 12 ? left : 12;
-        if (nb < 12) {   // the lane holding the end: drop the bytes behind it
-            const uint32_t keep = 0xFFFFFFFFu >> (8 * (3 - ((nb - 1) & 3)));
-            if (nb <= 4) { a0 &= keep; a1 = 0u; a2 = 0u; }
-            else if (nb <= 8) { a1 &= keep; a2 = 0u; }
-            else { a2 &= keep; }
-        }
+        a0 &= keep_low_bytes(nb);
+        a1 &= keep_low_bytes(nb - 4);
+        a2 &= keep_low_bytes(nb - 8);
         const uint4 v = encode12_mixed<(NLUT < 0 ? 0 : NLUT)>(a0, a1, a2, lut);
-        if (nb == 12) {
-            if (VEC16) {
-                *reinterpret_cast<uint4 *>(q) = v;
-            } else {
-                uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
-                q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
-            }
-        } else {
-            uint32_t w[4] = {v.x, v.y, v.z, v.w};
-            const int rem = nb % 3, gi = nb / 3;
-            if (rem) {
+        // nb = 3 gi + rem: group gi is the partial one; its last one or two characters become '='
+        const int gi = (nb * 11) >> 5, rem = nb - 3 * gi;
+        const uint32_t pm = rem == 1 ? 0xFFFF0000u : (rem == 2 ? 0xFF000000u : 0u);
+        uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-                for (int g = 0; g < 4; ++g)
-                    if (g == gi)
-                        w[g] = (rem == 1) ? ((w[g] & 0x0000FFFFu) | 0x3D3D0000u)
-                                          : ((w[g] & 0x00FFFFFFu) | 0x3D000000u);
-            }
-            const int nwords = (nb + 2) / 3;
+        for (int g = 0; g < 4; ++g) {
+            const uint32_t m = g == gi ? pm : 0u;
+            w[g] = (w[g] & ~m) | (0x3D3D3D3Du & m);
+        }
+        const int nwords = gi + (rem != 0);      // characters / 4
+        if (VEC16 && nwords == 4) {
+            *reinterpret_cast<uint4 *>(q) = make_uint4(w[0], w[1], w[2], w[3]);
+        } else {
             uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
 #pragma unroll
             for (int g = 0; g < 4; ++g)
@@ -870,125 +875,6 @@ __device__ __noinline__ void encode_group_staged(char *__restrict__ out, const u
         } else {
             if (ush & 3u) encode_stage<false, true, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
             else encode_stage<false, false, 1, NLUT, false>(ubuf, ush, udst, ulen, 0, lane, lut);
-        }
-    }
-}
-
-// A group tile whose unit offsets were staged with it: the tile's units are treated as ONE run of
-// 12-byte items (unit k contributes ceil(len_k / 12) of them) and consumer warp cw takes
-// warp-iterations cw, cw + kConsumerWarps, ... of that run, 32 items each, wherever the unit
-// boundaries fall.  Compared with one warp per unit (encode_group_tile) no lane idles in a unit's
-// last, partial iteration (a 2006-byte cloud-init text is 5.2 iterations), a warp's per-unit
-// set-up shrinks to three broadcast reads from shared memory, and an iteration that lies inside
-// one unit -- most of them -- runs the same code as a long unit's.  In an iteration that crosses a
-// boundary every lane gets its own (source, destination, bytes left); the lane holding a unit's
-// last item masks, pads with '=' and stores only the words it owns.
-//   s_in[k] = in_off[u0 + k] (k = 0..cnt), s_out[k] = out_off[u0 + k] (k = 0..cnt-1), shared memory.
-template <int kConsumerWarps, int NLUT>
-__device__ __noinline__ void encode_group_flat(char *__restrict__ out, const uint8_t *buf, uint32_t sh, int64_t tpos,
-                                               int cnt, int len, const int64_t *s_in, const int64_t *s_out,
-                                               int cw, int lane, const uint16_t *lut) {
-    // items of a unit: ceil(ulen / 12); units whose offsets are not sorted inside the tile get none
-    auto unit_items = [&](int64_t a, int64_t b) -> int {
-        const int64_t ulen = b - a;
-        if (ulen <= 0 || a < tpos || b > tpos + len) return 0;
-        return (int)(((uint32_t)ulen + 11u) / 12u);
-    };
-    int k = 0;                                   // the unit holding this warp's next item ...
-    int64_t ua = s_in[0], ub = s_in[1];
-    int un = unit_items(ua, ub), ustart = 0;     // ... its items, and the index of its first one
-    for (int item0 = cw * 32;; item0 += 32 * kConsumerWarps) {
-        while (item0 >= ustart + un) {           // warp-uniform walk
-            ustart += un;
-            if (++k >= cnt) return;
-            ua = ub;
-            ub = s_in[k + 1];
-            un = unit_items(ua, ub);
-        }
-        const int first = item0 - ustart;        // item of unit k this iteration starts with
-        if (un - first > 32 || (un - first == 32 && (int)(ub - ua) - 12 * (first + 31) == 12)) {
-            // ---- all 32 lanes inside unit k, every item whole: a long unit's inner loop
-            const uint32_t so = sh + (uint32_t)(ua - tpos) + 12u * (uint32_t)(first + lane);
-            const uint32_t *wp = reinterpret_cast<const uint32_t *>(buf + (so & ~3u));
-            const uint32_t s8 = (so & 3u) * 8;
-            uint32_t a0 = wp[0], a1 = wp[1], a2 = wp[2];
-            if (s8) {                            // uniform: every lane of a unit has the same phase
-                const uint32_t a3 = wp[3];
-                a0 = __funnelshift_r(a0, a1, s8);
-                a1 = __funnelshift_r(a1, a2, s8);
-                a2 = __funnelshift_r(a2, a3, s8);
-            }
-            const uint4 v = encode12_mixed<NLUT>(a0, a1, a2, lut);
-            char *q = out + s_out[k] + 16 * (int64_t)(first + lane);
-            const uint32_t qa = (uint32_t)(reinterpret_cast<uintptr_t>(q) & 15u);
-            if (qa == 0) {
-                *reinterpret_cast<uint4 *>(q) = v;
-            } else if ((qa & 3u) == 0) {
-                uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
-                q4[0] = v.x; q4[1] = v.y; q4[2] = v.z; q4[3] = v.w;
-            } else {
-                store_chars(q, v, 16);
-            }
-            continue;
-        }
-        // ---- the iteration meets the end of unit k: lanes are handed out unit by unit
-        uint32_t so = 0;
-        char *q = nullptr;
-        int left = 0;                            // bytes of its unit from this lane's item on; <= 0: idle lane
-        {
-            int assigned = 0, kk = k, f = first, n_items = un;
-            int64_t a = ua, b = ub;
-            for (;;) {
-                const int take = n_items - f < 32 - assigned ? n_items - f : 32 - assigned;
-                if (lane >= assigned && lane < assigned + take) {
-                    const int it = f + lane - assigned;
-                    so = sh + (uint32_t)(a - tpos) + 12u * (uint32_t)it;
-                    q = out + s_out[kk] + 16 * (int64_t)it;
-                    left = (int)(b - a) - 12 * it;
-                }
-                assigned += take;
-                if (assigned >= 32 || ++kk >= cnt) break;
-                a = b;
-                b = s_in[kk + 1];
-                n_items = unit_items(a, b);
-                f = 0;
-            }
-        }
-        if (left <= 0) continue;                 // (divergent from here on: a boundary iteration)
-        const uint32_t *wp = reinterpret_cast<const uint32_t *>(buf + (so & ~3u));
-        const uint32_t s8 = (so & 3u) * 8;
-        uint32_t a0 = wp[0], a1 = wp[1], a2 = wp[2];
-        const uint32_t a3 = wp[3];
-        a0 = __funnelshift_r(a0, a1, s8);
-        a1 = __funnelshift_r(a1, a2, s8);
-        a2 = __funnelshift_r(a2, a3, s8);
-        const int nb = left < 12 ? left : 12;    // bytes of this item
-        if (nb < 12) {                           // the unit's last item: drop the bytes behind it
-            const uint32_t keep = 0xFFFFFFFFu >> (8 * (3 - ((nb - 1) & 3)));
-            if (nb <= 4) { a0 &= keep; a1 = 0u; a2 = 0u; }
-            else if (nb <= 8) { a1 &= keep; a2 = 0u; }
-            else { a2 &= keep; }
-        }
-        const uint4 v = encode12_mixed<NLUT>(a0, a1, a2, lut);
-        uint32_t w[4] = {v.x, v.y, v.z, v.w};
-        const int rem = nb % 3, gi = nb / 3;
-        if (rem) {
-#pragma unroll
-            for (int g = 0; g < 4; ++g)
-                if (g == gi)
-                    w[g] = (rem == 1) ? ((w[g] & 0x0000FFFFu) | 0x3D3D0000u) : ((w[g] & 0x00FFFFFFu) | 0x3D000000u);
-        }
-        const uint32_t qa = (uint32_t)(reinterpret_cast<uintptr_t>(q) & 15u);
-        if (nb == 12 && qa == 0) {
-            *reinterpret_cast<uint4 *>(q) = make_uint4(w[0], w[1], w[2], w[3]);
-        } else if ((qa & 3u) == 0) {
-            const int nwords = (nb + 2) / 3;
-            uint32_t *q4 = reinterpret_cast<uint32_t *>(q);
-#pragma unroll
-            for (int g = 0; g < 4; ++g)
-                if (g < nwords) q4[g] = w[g];
-        } else {
-            store_chars(q, make_uint4(w[0], w[1], w[2], w[3]), (nb + 2) / 3 * 4);
         }
     }
 }
