@@ -618,11 +618,11 @@ def main():
         "gpu_launches_note": "per step: plan_count, plan_emit<0>, b64enc_groups (device-timed region)",
         "clocks": clocks,
     }
+    if distributed:
+        dist.destroy_process_group()      # before fd 1 comes back: NCCL reports its teardown on "stdout"
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)
-    if distributed:
-        dist.destroy_process_group()
     return 0
 
 
