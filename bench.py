@@ -623,6 +623,7 @@ def main():
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)
+    os.dup2(2, 1)                         # libraries that talk while the process exits (NCCL's plugin teardown) go to stderr too
     return 0
 
 
