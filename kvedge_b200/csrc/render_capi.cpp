@@ -506,6 +506,11 @@ int kv_helm_template(const char *chart_dir, const char *release_name, const char
 int kv_fleet_template(const kv_chart *chart, int n_releases, const char *const *release_names, const char *ns,
                       const kv_overrides *overrides, char **out, int64_t *out_off) {
     if (!chart || n_releases < 0 || !out || !out_off) return fail(KV_EINVAL, "null argument");
+    if (n_releases == 0) {   // nothing to render, nothing to encode
+        *out = static_cast<char *>(calloc(1, 1));
+        out_off[0] = 0;
+        return *out ? KV_OK : fail(KV_ENOMEM, "malloc");
+    }
 #ifdef KVEDGE_TOOLS
     const bool trace = getenv("KVEDGE_TRACE") && atoi(getenv("KVEDGE_TRACE")) > 0;   // tools build only
 #else

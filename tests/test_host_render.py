@@ -279,3 +279,23 @@ def test_cpu_twin_of_the_fleet_render_matches_the_oracle():
         ms, _ = helmref.split_manifests(helmref.render_files(ch, vals, name))
         ref = b"".join(b"---\n# Source: " + m.name.encode() + b"\n" + m.content + b"\n" for m in ms)
         assert stream[int(off[i]):int(off[i + 1])] == ref, name
+
+
+def test_fleet_render_fails_loudly_and_cleanly(tmp_path):
+    """kv_fleet_template's error paths end the call (no hang, no partial output): a template
+    error in one install of the fleet surfaces as TemplateError; on a machine without a CUDA
+    device the call plans on the host and then refuses to go on (no CPU fallback)."""
+    from kvedge_b200 import _lib
+    chart = helm.Chart(REF_CHART)
+    ok = [(f"r{i}", {"set": [f"nameOverride=site-{i}"], "blobs": {"azIotEdgeConfig": b"x = %d\n" % i}}) for i in range(40)]
+    bad = list(ok)
+    bad[17] = ("r17", {"set": ["azIotEdgeConfig=12345"]})          # b64enc of an int64: Helm aborts
+    with pytest.raises(helm.TemplateError, match="expected string"):
+        chart.template_fleet(bad)
+    if _lib.lib().kv_device_count() == 0:
+        with pytest.raises(helm.KvError, match="no CPU fallback|no CUDA device"):
+            chart.template_fleet(ok)
+    else:
+        got = chart.template_fleet(ok)
+        assert len(got) == 40 and got[3] == chart.template("r3", **ok[3][1])
+    assert chart.template_fleet([]) == []
