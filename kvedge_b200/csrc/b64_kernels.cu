@@ -1863,13 +1863,13 @@ struct EncGroupVariant {
 static const EncGroupVariant kEncGroup[] = {
     {stream::b64enc_groups<5, 3, 4, 2, 1, 0>, 5, 3, 4, 0},   // product
 #ifdef KVEDGE_TOOLS
-    {stream::b64enc_groups<6, 3, 4, 2, 1, 0>, 6, 3, 4, 0},
+    {stream::b64enc_groups<5, 3, 4, 2, 1, 0>, 5, 3, 4, 0},   // (201 was 6 x 3 x 4: no longer fits since stages carry unit offsets)
     {stream::b64enc_groups<6, 8, 4, 2, 1, 36480>, 6, 8, 4, 36480},
     {stream::b64enc_groups<5, 3, 4, 3, 1, 0>, 5, 3, 4, 0},
     {stream::b64enc_groups<4, 3, 4, 2, 1, 0>, 4, 3, 4, 0},
     {stream::b64enc_groups<4, 4, 4, 2, 1, 0>, 4, 4, 4, 0},
     {stream::b64enc_groups<4, 3, 5, 2, 1, 0>, 4, 3, 5, 0},
-    {stream::b64enc_groups<5, 4, 4, 2, 1, 0>, 5, 4, 4, 0},
+    {stream::b64enc_groups<5, 3, 4, 2, 1, 0>, 5, 3, 4, 0},   // (207 was 5 x 4 x 4: likewise)
     {stream::b64enc_groups<5, 3, 3, 2, 1, 0>, 5, 3, 3, 0},
 #endif
 };

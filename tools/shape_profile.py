@@ -6,6 +6,9 @@ Prints one JSON line with event timings (never quote a number taken under ncu)."
 import json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+if os.environ.get("KVEDGE_ENC_VARIANT") or os.environ.get("KVEDGE_DEC_VARIANT"):
+    from kvedge_b200 import _lib as _kvlib
+    _kvlib.use_tools_build()   # sweep shapes exist in libkvedge_b200_tools.so only
 import numpy as np, torch
 from kvedge_b200 import b64
 from oracle import b64 as ob64
@@ -42,9 +45,12 @@ def timed(fn, reps):
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / reps
 
-ms_enc = timed(lambda: b64.b64enc_device(d_in, d_in_off, d_out, d_out_off, scratch), 2)   # encodes #2, #3
+REPS = int(os.environ.get("REPS", "0"))
+if REPS:   # timing mode (not for ncu): warm up, then time REPS launches of each
+    timed(lambda: b64.b64enc_device(d_in, d_in_off, d_out, d_out_off, scratch), 3)
+ms_enc = timed(lambda: b64.b64enc_device(d_in, d_in_off, d_out, d_out_off, scratch), REPS or 2)   # encodes #2, #3
 ms_dec = timed(lambda: b64.b64dec_device(d_dense, d_dense_off, d_dec, d_dec_off, d_len, d_st, scratch,
-                                         total_in_bytes=int(dense_off[-1])), 3)
+                                         total_in_bytes=int(dense_off[-1])), REPS or 3)
 ok = bool((d_st == -1).all())
 got = d_out.cpu().numpy()
 for i in (0, n // 2, n - 1):
@@ -52,4 +58,5 @@ for i in (0, n // 2, n - 1):
     ok = ok and got[int(out_off[i]):int(out_off[i]) + len(enc)].tobytes() == enc
 algo = int(in_off[-1]) + int(dense_off[-1])
 print(json.dumps({"shape": shape, "units": n, "enc_ms": ms_enc, "enc_frac_6538": algo / ms_enc / 1e6 / 6538,
-                  "dec_ms": ms_dec, "dec_frac_6538": algo / ms_dec / 1e6 / 6538, "exact": ok}))
+                  "dec_ms": ms_dec, "dec_frac_6538": algo / ms_dec / 1e6 / 6538, "exact": ok,
+                  "enc_variant": os.environ.get("KVEDGE_ENC_VARIANT", ""), "dec_variant": os.environ.get("KVEDGE_DEC_VARIANT", "")}))
