@@ -471,9 +471,8 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
     return ok != 0;
 }
 // Wait with a deadline: a protocol bug must end in a trap (reported as a launch failure), never
-// in a hung GPU.  A waiting warp SLEEPS between polls: these kernels are bound by instruction
-// issue, and on short units two fifths of all issued instructions were polls of warps with
-// nothing to do (the producer ahead of its ring, consumers ahead of the producer).
+// in a hung GPU.  (Pointer form, used by the one-pipeline kernel for tiny batches: sleeps between
+// polls.)
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
@@ -510,16 +509,12 @@ __device__ __forceinline__ bool mbar_try_wait_hint_a(uint32_t bar, uint32_t pari
         : "=r"(ok) : "r"(bar), "r"(parity), "r"(hint_ns) : "memory");
     return ok != 0;
 }
-template <unsigned kFirstNs = 32, unsigned kMaxNs = 256>
+// What every wait of the grouped kernels uses.  On short units two fifths of all instructions the
+// first version issued were polls of warps with nothing to do (producers ahead of their ring,
+// consumers ahead of their producer).  Measured alternatives, all worse for at least one kernel:
+// nanosleep between polls (late wake-ups cost the decoder 1-3 points), polling without the clock
+// read (faster polling hurts every kernel).
 __device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
-    (void)kFirstNs; (void)kMaxNs;
-    if (mbar_try_wait_a(bar, parity)) return;
-    const long long t0 = clock64();
-    while (!mbar_try_wait_hint_a(bar, parity, 20000u))
-        if (clock64() - t0 > 8000000000ll) __trap();
-}
-// A producer waits for a ring slot, which takes the consumers microseconds to free.
-__device__ __forceinline__ void mbar_wait_slot(uint32_t bar, uint32_t parity) {
     if (mbar_try_wait_a(bar, parity)) return;
     const long long t0 = clock64();
     while (!mbar_try_wait_hint_a(bar, parity, 20000u))
@@ -961,10 +956,10 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
                 const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
                 uint32_t boff = s * kGroupStageStride;
                 if (kRing == 0) {
-                    mbar_wait_slot(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
+                    mbar_wait_a(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
                 } else {
                     while (waited + kStages <= c) {   // the barrier pair itself
-                        mbar_wait_slot(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                        mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                         ++waited;
                     }
                     // room for this tile (+ the 16 bytes a lane may read past its last byte)
@@ -978,7 +973,7 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
                         } else if (head + need <= tail) {                         // in flight: [tail, end) + [0, head)
                             break;
                         }
-                        mbar_wait_slot(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                        mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                         ++waited;
                     }
                     boff = head;
@@ -1038,10 +1033,10 @@ b64enc_groups(const uint8_t *__restrict__ in, char *__restrict__ out,
             // end-of-work stage, seen by every consumer warp of the group
             const uint32_t s = c % kStages;
             if (kRing == 0) {
-                mbar_wait_slot(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
+                mbar_wait_a(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
             } else {
                 while (waited + kStages <= c) {
-                    mbar_wait_slot(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                    mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                     ++waited;
                 }
             }
@@ -1501,11 +1496,11 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                 const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
                 uint32_t boff = s * kDecStageStride;
                 if (kRing == 0) {
-                    mbar_wait_a<0, 0>(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
+                    mbar_wait_a(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
                 } else {
                     // the barrier pair itself: tile c - kStages must be finished
                     while (waited + kStages <= c) {
-                        mbar_wait_a<0, 0>(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                        mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                         ++waited;
                     }
                     // room for this tile (+ the 16-byte chunk a lane may read past its last character)
@@ -1519,7 +1514,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
                         } else if (head + need <= tail) {                         // in flight: [tail, end) + [0, head)
                             break;
                         }
-                        mbar_wait_a<0, 0>(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                        mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                         ++waited;
                     }
                     boff = head;
@@ -1551,10 +1546,10 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
         if (lane == 0) {
             const uint32_t s = c % kStages;
             if (kRing == 0) {
-                mbar_wait_a<0, 0>(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
+                mbar_wait_a(empty_a + s * 8u, ((c / kStages) & 1u) ^ 1u);
             } else {
                 while (waited + kStages <= c) {
-                    mbar_wait_a<0, 0>(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
+                    mbar_wait_a(empty_a + (waited % kStages) * 8u, (waited / kStages) & 1u);
                     ++waited;
                 }
             }
@@ -1578,7 +1573,7 @@ b64dec_stream(const char *__restrict__ in, uint8_t *__restrict__ out,
             ((unsigned long long)(unsigned)header[5] << 32) | (unsigned long long)(unsigned)header[4]);
         uint32_t s = 0, ph = 0;
         for (;;) {
-            mbar_wait_a<0, 0>(full_a + s * 8u, ph);
+            mbar_wait_a(full_a + s * 8u, ph);
             const int4 hot = *reinterpret_cast<const int4 *>(&gmeta[s]);
             const int len = hot.z;
             if (len < 0) break;
