@@ -9,6 +9,9 @@ sys.path.insert(0, ROOT)
 if os.environ.get("KVEDGE_ENC_VARIANT") or os.environ.get("KVEDGE_DEC_VARIANT"):
     from kvedge_b200 import _lib as _kvlib
     _kvlib.use_tools_build()   # sweep shapes exist in libkvedge_b200_tools.so only
+if os.environ.get("KVEDGE_LIB"):   # an experimental build of the library, by path
+    from kvedge_b200 import _lib as _kvlib2
+    _kvlib2._path = os.environ["KVEDGE_LIB"]
 import numpy as np, torch
 from kvedge_b200 import b64
 from oracle import b64 as ob64
