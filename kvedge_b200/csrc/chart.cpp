@@ -824,12 +824,22 @@ void sorted_docs(const std::vector<std::pair<const std::string *, const std::str
         }
         emit(start, b);
     }
-    std::stable_sort(docs->begin(), docs->end(), [](const DocRef &x, const DocRef &y) {
+    auto before = [](const DocRef &x, const DocRef &y) {
         if (x.rank < 0 && y.rank < 0) return x.kind < y.kind;  // unknown kinds: alphabetical, stable within a kind
         if (x.rank < 0) return false;
         if (y.rank < 0) return true;
         return x.rank < y.rank;
-    });
+    };
+    if (docs->size() <= 32) {   // a chart's handful of documents: stable insertion sort, no temporary buffer
+        for (size_t i = 1; i < docs->size(); ++i) {
+            size_t j = i;
+            while (j > 0 && before((*docs)[i], (*docs)[j - 1])) --j;
+            if (j != i) std::rotate(docs->begin() + (std::ptrdiff_t)j, docs->begin() + (std::ptrdiff_t)i,
+                                    docs->begin() + (std::ptrdiff_t)i + 1);
+        }
+    } else {
+        std::stable_sort(docs->begin(), docs->end(), before);
+    }
 }
 
 }  // namespace
@@ -848,8 +858,8 @@ void split_manifests(const std::map<std::string, std::string> &files, std::vecto
 
 void frame_manifests(const std::vector<std::pair<const std::string *, const std::string *>> &files,
                      std::string *manifest, std::string *notes) {
-    std::vector<DocRef> docs;
-    docs.reserve(files.size());
+    static thread_local std::vector<DocRef> docs;   // capacity kept per thread: a fleet frames thousands of releases
+    docs.clear();
     const std::string *n = nullptr;
     sorted_docs(files, &docs, &n);
     size_t total = 0;

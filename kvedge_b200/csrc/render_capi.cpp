@@ -226,8 +226,8 @@ void render_files(const kv_chart *c, const Value &vals, const char *release, con
 }
 
 void frame(const kv_chart *c, const std::vector<std::string> &rendered, std::string *manifest, std::string *notes) {
-    std::vector<std::pair<const std::string *, const std::string *>> files;
-    files.reserve(rendered.size());
+    static thread_local std::vector<std::pair<const std::string *, const std::string *>> files;
+    files.clear();
     for (size_t k = 0; k < rendered.size(); ++k) files.push_back({&c->files[k].name, &rendered[k]});
     kvedge::chart::frame_manifests(files, manifest, notes);
 }
@@ -356,6 +356,7 @@ int plan_release(const kv_chart *c, const char *release, const char *ns, const k
     bool user_sentinels = false;
     Value vals = merged_values(c, ov, &user_sentinels);
     const bool can_defer = defer && !c->templates_have_sentinels && !c->defaults_have_sentinels && !user_sentinels;
+    r->pending.reserve(4);
     static thread_local std::vector<std::string> rendered;   // per-file output, capacity kept per thread
     render_files(c, vals, release, ns, can_defer, &r->pending, &rendered, &r->keepalive);
     frame(c, rendered, &r->manifest, &r->notes);
