@@ -1,7 +1,7 @@
 """GPU parity of the whole drop-in path: chart -> C++ engine -> pending b64enc sites encoded
 on the GPU -> `helm template` stream, against the oracle's render of the same chart.
-/root/reference does not exist on the GPU box, so these run on the repo's own fixture chart
-(the reference chart is covered by the hash goldens in tests/test_host_render.py)."""
+These run on the repo's own fixture chart (range/with/maps/lists, immediate b64enc sites); the
+reference's chart itself runs through the same path in tests/test_gpu_reference_chart.py."""
 import os
 
 import pytest
