@@ -279,27 +279,6 @@ size_t expand_into(char *dst, const std::string &text, const std::vector<Pending
     return (size_t)(q - dst);
 }
 
-// Run fn(i) for i in [0, n) on all host threads.
-template <typename F>
-void parallel_for(int n, F fn) {
-    unsigned n_thr = std::thread::hardware_concurrency();
-    if (n_thr == 0) n_thr = 1;
-    if (n_thr > 64) n_thr = 64;
-    if ((int)n_thr > n) n_thr = (unsigned)(n > 0 ? n : 1);
-    std::atomic<int> next{0};
-    auto work = [&]() {
-        for (;;) {
-            const int b = next.fetch_add(16);
-            if (b >= n) return;
-            for (int i = b; i < n && i < b + 16; ++i) fn(i);
-        }
-    };
-    std::vector<std::thread> pool;
-    for (unsigned t = 1; t < n_thr; ++t) pool.emplace_back(work);
-    work();
-    for (auto &t : pool) t.join();
-}
-
 // The buffer kv_fleet_template hands out.  A fleet's stream is tens of megabytes: fresh from
 // malloc it arrives as untouched pages and the first write to each of them is a page fault (more
 // time than the encode).  So the last buffer given back through kv_free is kept (one per process)
