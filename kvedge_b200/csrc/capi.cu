@@ -380,7 +380,7 @@ int kv_set_last_error_(int code, const char *msg) {
     return code;
 }
 
-int kv_version(void) { return 100; }
+int kv_version(void) { return 200; }  // 0.2.0: kv_b64_batch_status_dev, kv_host_pipeline_config
 
 const char *kv_last_error(void) { return g_err.c_str(); }
 
